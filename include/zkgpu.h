@@ -1,0 +1,108 @@
+/* zkgpu.h — C ABI of libzkgpu.so: the B200 (sm_100a) implementation of zkevm-prover's STARK commit hot path
+ * (Goldilocks NTT / INTT / extendPol + Poseidon-Goldilocks Merkle tree).
+ *
+ * The reference has no FFI layer for this path: starkpil links the C++ classes NTT_Goldilocks,
+ * PoseidonGoldilocks and MerkleTreeGL directly.  include/ntt_goldilocks.hpp, include/poseidon_goldilocks.hpp
+ * and include/merkleTreeGL.hpp re-declare those classes with identical signatures and forward to the
+ * entry points below; each entry point cites the reference interface it replaces
+ * (paths relative to the reference repository root).
+ *
+ * Conventions
+ *   - Every data pointer may be a HOST pointer (pageable or pinned) or a DEVICE pointer of the current
+ *     device; the library detects which (cudaPointerGetAttributes).  Host data is staged through device
+ *     memory; device data is used in place.  All pointers of one call must be of the same kind.
+ *   - Elements are uint64_t words of the Goldilocks field p = 2^64 - 2^32 + 1.  Inputs may be any 64-bit
+ *     word (the reference accepts non-canonical words); every output word is canonical (< p), i.e. equal
+ *     to Goldilocks::toU64 of the reference's output (goldilocks_base_field_tools.hpp:152-163).
+ *   - Return value: 0 on success, < 0 on error; zkgpu_last_error() gives the message (thread local).
+ *   - Calls are synchronous with respect to the host when given host pointers.  With device pointers the
+ *     work is enqueued on the library stream (zkgpu_set_stream) and the call returns without waiting.
+ *   - There is no CPU fallback: without a usable CUDA device every compute entry point fails.
+ */
+#ifndef ZKGPU_H
+#define ZKGPU_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ---- */
+int zkgpu_init(int device);            /* select the device (-1 = keep the current one) and create the context */
+int zkgpu_set_stream(void *cuda_stream); /* cudaStream_t to enqueue on; NULL = the library's own stream */
+int zkgpu_sync(void);                  /* wait for everything enqueued on the library stream */
+const char *zkgpu_last_error(void);
+int zkgpu_device_count(void);
+int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes);
+/* device-memory helpers so that C/C++ hosts need no CUDA headers */
+int zkgpu_malloc(void **dev_ptr, uint64_t bytes);
+int zkgpu_free(void *dev_ptr);
+int zkgpu_malloc_host(void **host_ptr, uint64_t bytes); /* pinned */
+int zkgpu_free_host(void *host_ptr);
+int zkgpu_memcpy(void *dst, const void *src, uint64_t bytes); /* any direction, synchronous */
+/* device timings (ms, CUDA events) of the stages of the last commit-type call on this thread's context:
+ * [0] LDE (STARK_STEP_k_LDE), [1] Merkle leaves, [2] Merkle node levels (STARK_STEP_k_MERKLETREE = [1]+[2]),
+ * [3] host->device staging, [4] device->host staging.  Waits for the stream. */
+int zkgpu_stage_ms(float out[5]);
+
+/* synthetic input generator shared with the CPU oracle: dst[i] = splitmix64(seed + offset + i) mod p */
+int zkgpu_fill(uint64_t *dst, uint64_t n, uint64_t seed, uint64_t offset);
+
+/* element-wise field ops on n words (KAT hook for the device arithmetic that replaces
+ * goldilocks_base_field_scalar.hpp:16-160): op 0 = add, 1 = sub, 2 = mul, 3 = mul (un-normalised path, then toU64),
+ * 4 = toU64.  Operands may be any 64-bit words; results are canonical. */
+int zkgpu_field_op(int op, uint64_t *out, const uint64_t *a, const uint64_t *b, uint64_t n);
+
+/* ---- NTT_Goldilocks (src/goldilocks/src/ntt_goldilocks.hpp:49-136 ctor, :166-173 methods) ---- */
+/* NTT_Goldilocks(maxDomainSize, nThreads, extension): returns NULL (and sets the error) if log2(maxDomainSize) > 32,
+ * where the reference throws std::range_error (ntt_goldilocks.hpp:94-97). */
+void *zkgpu_ntt_create(uint64_t max_domain_size, int extension);
+void zkgpu_ntt_destroy(void *ntt);
+/* NTT_Goldilocks::NTT / ::INTT (ntt_goldilocks.cpp:166-232, 307-324).  dst == NULL or dst == src: in place.
+ * size must be a power of two (the reference asserts, ntt_goldilocks.cpp:28); size == 0 or ncols == 0: no-op.
+ * inverse: INTT (scaled by 1/size); extend (inverse only): additionally row i is multiplied by 7^i, i.e. the
+ * reference's r_[i] = 7^i / size (ntt_goldilocks.hpp:153-165).  buffer/nphase/nblock of the reference are CPU
+ * blocking knobs: buffer is accepted and not used. */
+int zkgpu_ntt(void *ntt, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, uint64_t *buffer, int inverse,
+              int extend);
+/* NTT_Goldilocks::extendPol (ntt_goldilocks.cpp:326-352): output (N_Extended x ncols) = evaluations on the coset
+ * 7*<w_NExt> of the polynomials interpolating the N x ncols input columns.  output == input is allowed. */
+int zkgpu_extend_pol(void *ntt, uint64_t *output, const uint64_t *input, uint64_t n_extended, uint64_t n, uint64_t ncols,
+                     uint64_t *buffer);
+
+/* ---- PoseidonGoldilocks (src/goldilocks/src/poseidon_goldilocks.hpp:43-81) ---- */
+/* hash_full_result (poseidon_goldilocks.cpp:166-228): n independent 12-word permutations */
+int zkgpu_hash_full_result(uint64_t *out12, const uint64_t *in12, uint64_t n);
+/* linear_hash (poseidon_goldilocks.cpp:229-265): 4-word digest of `size` words (size <= 4: copy, not hashed) */
+int zkgpu_linear_hash(uint64_t *out4, const uint64_t *input, uint64_t size);
+/* merkletree / merkletree_avx (poseidon_goldilocks.hpp:74-81, .cpp:266-301): tree has (2*num_rows - 1) * 4 words,
+ * leaves first then each level (MerklehashGoldilocks::getTreeNumElements, merklehash_goldilocks.hpp:15-28).
+ * num_rows must be a power of two (the reference's loop is only well defined then); num_rows == 0: no-op. */
+int zkgpu_merkletree(uint64_t *tree, const uint64_t *input, uint64_t num_cols, uint64_t num_rows, uint64_t dim);
+/* merkletree_batch (poseidon_goldilocks.cpp:302-352) */
+int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size,
+                           uint64_t dim);
+
+/* ---- the commit stage as one call: Starks::genProof steps 1-3 (src/starkpil/starks.cpp:51-58, 133-139, 214-220):
+ * ntt.extendPol(out_ext, in, NExt, N, ncols) followed by MerkleTreeGL(NExt, ncols, out_ext).merkelize().
+ * out_ext: n_extended x ncols, tree: (2*n_extended - 1)*4 words.  With host pointers the trace is streamed
+ * through the device in column strips. */
+int zkgpu_extend_and_merkelize(void *ntt, uint64_t *out_ext, uint64_t *tree, const uint64_t *input, uint64_t n_extended,
+                               uint64_t n, uint64_t ncols);
+
+/* ---- multi-GPU building blocks (device pointers only; one process per GPU, the host side does the exchange) ----
+ * LDE of a column shard stored with an arbitrary row stride (columns are independent, ntt_goldilocks.cpp:103-110) */
+int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64_t in_ld, uint64_t n_extended, uint64_t n,
+                      uint64_t ncols);
+/* leaf digests of a row shard (poseidon_goldilocks.cpp:277-281): leaves[4*i..] = linear_hash(row i) */
+int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_words, uint64_t row_ld, uint64_t num_rows);
+/* node levels above num_rows leaves already stored at tree[0 .. 4*num_rows) (poseidon_goldilocks.cpp:283-300) */
+int zkgpu_merkle_levels(uint64_t *tree, uint64_t num_rows);
+/* gather/scatter between a row-major matrix and a packed block: dst[r*ncols + c] = src[(row0 + r)*src_ld + col0 + c]
+ * (pack) or the inverse (unpack) — used around the column-shard -> row-shard all-to-all */
+int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64_t src_ld, uint64_t nrows, uint64_t ncols);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZKGPU_H */

@@ -1,0 +1,332 @@
+"""GPU parity tests: libzkgpu.so (CUDA, through the C ABI / the Python mirror of the reference classes) against the
+CPU oracle (oracle/gl_oracle.c), the reference's own known-answer vectors (tests/golden/reference_kats.json) and the
+committed outputs of the compiled reference (tests/golden/reference_diff.json).  Bit-exact on canonical words.
+Mirrors src/goldilocks/tests/tests.cpp: poseidon_full_avx (:1627), linear_hash_avx (:1767), merkletree_avx (:1883),
+ntt / ntt_block (:2225-2384), LDE (:2385), LDE_block (:2467), extendePol (:2554)."""
+import numpy as np
+import pytest
+
+import zkevm_prover_b200 as zk
+from oracle_lib import Oracle, P, SEED, digest, load_golden, hexwords, field_fib, merkle_kat_matrix
+
+pytestmark = pytest.mark.gpu
+
+O = Oracle()
+KATS = load_golden("reference_kats.json")
+DIFF = load_golden("reference_diff.json")
+
+
+def u64(x):
+    return np.ascontiguousarray(x, dtype=np.uint64)
+
+
+def first_diff(a, b):
+    a, b = np.asarray(a).reshape(-1), np.asarray(b).reshape(-1)
+    idx = np.nonzero(a != b)[0]
+    if idx.size == 0:
+        return "equal"
+    i = int(idx[0])
+    return "%d of %d words differ; first at %d: got %016x want %016x" % (idx.size, a.size, i, int(a[i]), int(b[i]))
+
+
+def addmod(a, b):
+    """(a + b) mod p for canonical uint64 arrays."""
+    s = a + b
+    s = np.where(s < a, s + np.uint64(0xFFFFFFFF), s)
+    return np.where(s >= np.uint64(P), s - np.uint64(P), s)
+
+
+def assert_eq(got, want, what=""):
+    assert np.array_equal(np.asarray(got).reshape(-1), np.asarray(want).reshape(-1)), what + " " + first_diff(got, want)
+
+
+def gpu_ntt(a, inverse=False, extend=False):
+    a = u64(a)
+    n, c = a.shape
+    ntt = zk.NTT_Goldilocks(n)
+    out = np.zeros_like(a)
+    ntt.NTT(out, a, n, c, None, 3, 1, inverse, extend)
+    return out
+
+
+def gpu_extend(a, n_ext):
+    a = u64(a)
+    n, c = a.shape
+    ntt = zk.NTT_Goldilocks(n)
+    out = np.zeros((n_ext, c), dtype=np.uint64)
+    ntt.extendPol(out, a, n_ext, n, c)
+    return out
+
+
+def gpu_tree(a, ncols, nrows, dim=1, batch=0):
+    tree = np.zeros((2 * nrows - 1) * 4, dtype=np.uint64)
+    a = u64(a)
+    if batch:
+        zk.PoseidonGoldilocks.merkletree_batch(tree, a, ncols, nrows, batch, 0, dim)
+    else:
+        zk.PoseidonGoldilocks.merkletree(tree, a, ncols, nrows, 0, dim)
+    return tree
+
+
+# ------------------------------------------------------------------------------------------------ field
+def test_field_ops_edges_and_random():
+    """goldilocks_base_field_scalar.hpp:16-160 semantics (value class mod p) incl. non-canonical operands."""
+    edge = [0, 1, 2, 7, 0xFFFFFFFF, 0x100000000, 0x100000001, 2**32 - 2, P - 1, P, P + 1, P - 2, 2**63, 2**63 - 1,
+            0xFFFFFFFF00000000, 0xFFFFFFFEFFFFFFFF, 2**64 - 1, 2**64 - 2, 0x00000001FFFFFFFF, 0x7FFFFFFF80000001]
+    A = [a for a in edge for _ in edge]
+    B = [b for _ in edge for b in edge]
+    rng = np.random.default_rng(3)
+    ra = rng.integers(0, 2**63, size=200000, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=200000, dtype=np.uint64)
+    rb = rng.integers(0, 2**63, size=200000, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=200000, dtype=np.uint64)
+    # bias some operands to the top of the range where the carry fix-ups trigger
+    ra[:50000] |= np.uint64(0xFFFFFFFF00000000)
+    rb[25000:75000] |= np.uint64(0xFFFFFFFF00000000)
+    a = np.concatenate([np.array(A, dtype=np.uint64), ra])
+    b = np.concatenate([np.array(B, dtype=np.uint64), rb])
+    ai = [int(x) for x in a]
+    bi = [int(x) for x in b]
+    for op, f in (("add", lambda x, y: (x + y) % P), ("sub", lambda x, y: (x - y) % P), ("mul", lambda x, y: (x * y) % P),
+                  ("mul_nc", lambda x, y: (x * y) % P), ("canon", lambda x, y: x % P)):
+        got = zk.field_op(op, a, b)
+        want = np.array([f(x, y) for x, y in zip(ai, bi)], dtype=np.uint64)
+        assert_eq(got, want, op)
+
+
+# ------------------------------------------------------------------------------------------------ poseidon
+def test_poseidon_kats():
+    out = np.zeros(12, dtype=np.uint64)
+    zk.PoseidonGoldilocks.hash_full_result(out, field_fib(12, 0, 1))
+    assert_eq(out, hexwords(KATS["poseidon_fibonacci"]["expected"]), "fibonacci")
+    zk.PoseidonGoldilocks.hash_full_result(out, np.zeros(12, dtype=np.uint64))
+    assert_eq(out, hexwords(KATS["poseidon_zero"]["expected"]), "zero")
+
+
+def test_poseidon_random_and_noncanonical_states():
+    rng = np.random.default_rng(11)
+    n = 4096
+    st = rng.integers(0, 2**63, size=(n, 12), dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+    st[0, :] = np.uint64(2**64 - 1)
+    st[1, :] = np.uint64(P)
+    st[2, :] = np.uint64(P - 1)
+    st[3, :] = 0
+    out = np.zeros_like(st)
+    zk.PoseidonGoldilocks.hash_full_result(out, st, n)
+    want = np.stack([O.hash_full_result(st[i]) for i in range(n)])
+    assert_eq(out, want)
+
+
+def test_linear_hash_kat_and_lengths():
+    out = np.zeros(4, dtype=np.uint64)
+    zk.PoseidonGoldilocks.linear_hash(out, field_fib(128, 0, 1), 128)
+    assert_eq(out, hexwords(KATS["linear_hash_fib128"]["expected"]))
+    rng = np.random.default_rng(5)
+    for n in [0, 1, 2, 3, 4, 5, 7, 8, 9, 15, 16, 17, 84 * 8, 665, 751, 1000]:
+        x = rng.integers(0, 2**63, size=max(n, 1), dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+        zk.PoseidonGoldilocks.linear_hash(out, x, n)
+        assert_eq(out, O.linear_hash(x[:n]), "n=%d" % n)
+
+
+def test_merkle_root_kats():
+    m = merkle_kat_matrix(64, 128)
+    t = gpu_tree(m, 128, 64)
+    assert_eq(t[-4:], hexwords(KATS["merkle_root_64x128"]["expected"]))
+    assert_eq(t, O.merkletree(m, 128, 64), "all nodes")
+    tb = gpu_tree(m, 128, 64, batch=32)
+    assert_eq(tb[-4:], hexwords(KATS["merkle_batch_root_64x128_b32"]["expected"]))
+    e = np.zeros(1, dtype=np.uint64)
+    assert_eq(gpu_tree(e, 0, 64)[-4:], hexwords(KATS["merkle_root_ncols0_64"]["expected"]))
+    assert_eq(gpu_tree(e, 0, 1 << 17)[-4:], hexwords(KATS["merkle_root_ncols0_131072"]["expected"]))
+
+
+def test_merkletree_shapes_vs_oracle():
+    rng = np.random.default_rng(9)
+    for rows, c, dim, batch in [(1, 8, 1, 0), (2, 3, 1, 0), (64, 13, 1, 0), (32, 5, 3, 0), (128, 3, 1, 0), (128, 4, 1, 0),
+                                (16, 50, 1, 16), (8, 0, 1, 0), (256, 665, 1, 0), (64, 12, 3, 5), (1024, 9, 1, 0)]:
+        a = rng.integers(0, 2**63, size=(rows, max(c * dim, 1)), dtype=np.uint64) * np.uint64(2)
+        assert_eq(gpu_tree(a, c, rows, dim, batch), O.merkletree(a, c, rows, dim, batch), str((rows, c, dim, batch)))
+
+
+def test_merkle_tree_class_and_group_proof():
+    """MerkleTreeGL (merkleTreeGL.cpp:12-44): merkelize, getRoot, getGroupProof verify against the root."""
+    h, w = 256, 20
+    src = O.fill(h * w, SEED, 5)
+    mt = zk.MerkleTreeGL(h, w, src)
+    mt.merkelize()
+    assert_eq(mt.nodes, O.merkletree(src, w, h))
+    for idx in (0, 1, 77, 255):
+        proof = mt.getGroupProof(idx)
+        assert proof.size == w + 4 * mt.MerkleProofSize()
+        node = O.linear_hash(proof[:w])
+        i = idx
+        for lvl in range(mt.MerkleProofSize()):
+            sib = proof[w + 4 * lvl: w + 4 * lvl + 4]
+            pair = [node, sib] if i % 2 == 0 else [sib, node]
+            st = np.concatenate(pair + [np.zeros(4, dtype=np.uint64)])
+            node = O.hash_full_result(st)[:4]
+            i >>= 1
+        assert_eq(node, mt.getRoot(), "proof idx %d" % idx)
+
+
+# ------------------------------------------------------------------------------------------------ ntt
+def test_ntt_all_pass_sizes_vs_oracle():
+    """forward / inverse / inverse+extend for every log size 0..13 (every in-tile radix split and 1-2 pass plans)."""
+    for lg in range(0, 14):
+        n = 1 << lg
+        for c in (1, 3, 17):
+            a = O.fill(n * c, SEED, lg * 100 + c).reshape(n, c)
+            assert_eq(gpu_ntt(a), O.ntt(a), "ntt lg=%d c=%d" % (lg, c))
+            assert_eq(gpu_ntt(a, inverse=True), O.intt(a), "intt lg=%d c=%d" % (lg, c))
+            assert_eq(gpu_ntt(a, inverse=True, extend=True), O.intt(a, extend=True), "intt-extend lg=%d c=%d" % (lg, c))
+
+
+def test_ntt_three_pass_plans_vs_oracle():
+    for lg, c in [(17, 5), (18, 2), (20, 1)]:
+        n = 1 << lg
+        a = O.fill(n * c, SEED, lg).reshape(n, c)
+        assert_eq(gpu_ntt(a), O.ntt(a), "ntt lg=%d" % lg)
+        assert_eq(gpu_ntt(a, inverse=True), O.intt(a), "intt lg=%d" % lg)
+
+
+def test_ntt_roundtrip_reference_cases():
+    """tests.cpp:2225-2384: NTT then INTT is the identity; dst NULL / dst == src / dst != src; size 0, ncols 0 no-ops."""
+    ntt = zk.NTT_Goldilocks(1 << 12)
+    for n, c in [(16, 1), (16, 8), (1, 3), (2, 3), (1 << 12, 7)]:
+        a = O.fill(n * c, SEED, 77).reshape(n, c)
+        b = a.copy()
+        ntt.NTT(None, b, n, c)          # in place (dst NULL)
+        ntt.INTT(b, b, n, c)            # dst == src
+        assert_eq(b, a, "in-place roundtrip %s" % ((n, c),))
+        d = np.zeros_like(a)
+        ntt.NTT(d, a, n, c, None, 4, 3)  # nphase / nblock accepted
+        e = np.zeros_like(a)
+        ntt.INTT(e, d, n, c, None, 3, 5)
+        assert_eq(e, a, "out-of-place roundtrip")
+    z = np.zeros(4, dtype=np.uint64)
+    ntt.NTT(z, z, 0, 1)
+    ntt.NTT(z, z, 4, 0)
+    ntt.extendPol(z, z, 8, 4, 0)
+    with pytest.raises(zk.ZkGpuError):
+        ntt.NTT(z, z, 3, 1)
+    with pytest.raises(OverflowError):
+        zk.NTT_Goldilocks(1 << 33)
+
+
+def test_lde_kats():
+    # LDE with shift 49 (tests.cpp:2385-2461): INTT, scale by 49^i, zero pad, NTT 32
+    a = field_fib(16, 1, 1).reshape(16, 1)
+    c = gpu_ntt(a, inverse=True)
+    c = np.array([(int(c[i, 0]) * pow(49, i, P)) % P for i in range(16)] + [0] * 16, dtype=np.uint64).reshape(32, 1)
+    assert_eq(gpu_ntt(c)[:, 0], hexwords(KATS["lde_shift49_16to32"]["expected"]), "LDE shift 49")
+    # extendPol 16x8 -> 32x8 (tests.cpp:2554-2611), out of place and in place (a, a)
+    m = np.stack([field_fib(16, 1 + j, 1 + j) for j in range(8)], axis=1)
+    e = gpu_extend(m, 32)
+    assert_eq(e[:, 0], hexwords(KATS["extendpol_16x8_col0"]["expected"]), "extendPol KAT")
+    buf = np.zeros((32, 8), dtype=np.uint64)
+    buf[:16] = m
+    zk.NTT_Goldilocks(16).extendPol(buf, buf, 32, 16, 8)
+    assert_eq(buf, e, "extendPol in place")
+
+
+def test_extend_pol_vs_oracle_shapes():
+    rng = np.random.default_rng(21)
+    for n, c, b in [(1, 3, 2), (2, 1, 2), (64, 3, 2), (1 << 11, 9, 2), (32, 12, 16), (256, 17, 8), (1 << 10, 665, 2), (1 << 9, 5, 1),
+                    (1 << 13, 33, 4), (1 << 16, 8, 2)]:
+        a = rng.integers(0, 2**63, size=(n, c), dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=(n, c), dtype=np.uint64)
+        assert_eq(gpu_extend(a, n * b), O.extend_pol(a, n * b), "extendPol %s" % ((n, c, b),))
+
+
+def test_committed_reference_outputs():
+    """tests/golden/reference_diff.json: outputs of the compiled unmodified reference on seeded inputs."""
+    for case in DIFF["cases"]:
+        op = case["op"]
+        if op == "extend_and_merkelize":
+            n, c, b = case["n"], case["ncols"], case["blowup"]
+            a = O.fill(n * c, SEED, 0).reshape(n, c)
+            ext = np.zeros((n * b, c), dtype=np.uint64)
+            tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
+            zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n * b, n, c)
+            assert digest(ext) == case["ext_sha256"], case
+            assert digest(tree) == case["tree_sha256"], case
+            assert_eq(tree[-4:], hexwords(case["root"]))
+        elif op in ("ntt", "intt"):
+            n, c = case["n"], case["ncols"]
+            a = O.fill(n * c, SEED, 1).reshape(n, c)
+            assert digest(gpu_ntt(a, inverse=(op == "intt"))) == case["sha256"], case
+        elif op in ("merkletree", "merkletree_batch"):
+            rows, c, dim, batch = case["rows"], case["ncols"], case["dim"], case["batch"]
+            a = O.fill(rows * c * dim, SEED, 2).reshape(rows, c * dim)
+            assert digest(gpu_tree(a, c, rows, dim, batch)) == case["tree_sha256"], case
+        elif op == "noncanonical":
+            n, c = case["n"], case["ncols"]
+            a = O.fill(n * c, SEED, 3).reshape(n, c)
+            a[0, :] = P
+            a[1, :] = P + 1
+            a[2, :] = 2**64 - 1
+            a[3, :] = P - 1
+            assert digest(gpu_extend(a, 2 * n)) == case["ext_sha256"]
+            assert digest(gpu_tree(a, c, n)) == case["tree_of_input_sha256"]
+
+
+# ------------------------------------------------------------------------------------------------ device-resident path
+def _dev(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.int64)).cuda()
+
+
+def _host(t):
+    return t.cpu().numpy().view(np.uint64)
+
+
+def test_device_pointer_commit_matches_oracle():
+    """config #1 of BASELINE.json (2^16 x 8, blowup 2) through the fused call with DEVICE pointers, plus the on-device
+    generator: extended trace, every tree node and the root equal the oracle."""
+    import torch
+    n, c, b = 1 << 16, 8, 2
+    d_in = torch.empty(n * c, dtype=torch.int64, device="cuda")
+    zk.fill(d_in, n * c, SEED, 0)
+    zk.sync()
+    a = O.fill(n * c, SEED, 0)
+    assert_eq(_host(d_in), a, "generator")
+    d_ext = torch.empty(n * b * c, dtype=torch.int64, device="cuda")
+    d_tree = torch.empty((2 * n * b - 1) * 4, dtype=torch.int64, device="cuda")
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), d_ext, d_tree, d_in, n * b, n, c)
+    ms = zk.stage_ms()
+    assert ms["lde"] > 0 and ms["leaves"] > 0
+    ext = O.extend_pol(a.reshape(n, c), n * b)
+    assert_eq(_host(d_ext), ext, "extended trace")
+    assert_eq(_host(d_tree), O.merkletree(ext, c, n * b), "tree")
+
+
+def test_narrow_high_blowup_shape():
+    """config #4 shape class (12 cols, blowup 16) at 2^13 rows."""
+    n, c, b = 1 << 13, 12, 16
+    a = O.fill(n * c, SEED, 4).reshape(n, c)
+    ext = np.zeros((n * b, c), dtype=np.uint64)
+    tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n * b, n, c)
+    want = O.extend_pol(a, n * b)
+    assert_eq(ext, want, "ext")
+    assert_eq(tree, O.merkletree(want, c, n * b), "tree")
+
+
+def test_strip_path_and_properties_large():
+    """A shape wide/tall enough to take several column strips when the scratch budget is small is covered by forcing
+    strided shards: LDE of a column shard with ld > ncols equals the same columns of the full LDE (columns are
+    independent), and linearity LDE(a + b) = LDE(a) + LDE(b) holds at 2^18 x 24."""
+    import torch
+    n, c, b = 1 << 18, 24, 2
+    x = O.fill(n * c, SEED, 8)
+    y = O.fill(n * c, SEED, 9)
+    s = addmod(x, y)
+    ex, ey, es = gpu_extend(x.reshape(n, c), n * b), gpu_extend(y.reshape(n, c), n * b), gpu_extend(s.reshape(n, c), n * b)
+    want = addmod(ex, ey)
+    assert_eq(es, want, "linearity")
+    # column shard with strides
+    d_in = _dev(x)
+    d_out = torch.zeros(n * b * 7, dtype=torch.int64, device="cuda")
+    rc = zk.lib().zkgpu_lde_columns(d_out.data_ptr(), 7, d_in.data_ptr() + 8 * 5, c, n * b, n, 7)
+    assert rc == 0, zk.lib().zkgpu_last_error()
+    zk.sync()
+    assert_eq(_host(d_out).reshape(n * b, 7), ex[:, 5:12], "column shard")
+    # spot-check against the oracle on 3 columns
+    assert_eq(ex[:, :3], O.extend_pol(np.ascontiguousarray(x.reshape(n, c)[:, :3]), n * b), "oracle spot check")

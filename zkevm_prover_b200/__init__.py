@@ -1,0 +1,244 @@
+"""zkevm_prover_b200 — host-side Python mirror of the reference's commit-stage classes over libzkgpu.so.
+
+The product is the CUDA library (csrc/ -> libzkgpu.so, C ABI in include/zkgpu.h) and the C++ drop-in headers in
+include/.  This module binds the same C ABI with ctypes and mirrors the reference's class surface
+(NTT_Goldilocks, PoseidonGoldilocks, MerkleTreeGL: same method names, argument order and defaults as
+src/goldilocks/src/ntt_goldilocks.hpp:49,166-173, src/goldilocks/src/poseidon_goldilocks.hpp:43-81 and
+src/starkpil/merkleTree/merkleTreeGL.hpp:17-78) so that tests and the benchmark read like the reference's.
+
+There is no CPU fallback: importing works anywhere (so that the CPU test-suite can check the ABI), but every
+compute call fails with ZkGpuError when the library or a CUDA device is missing.
+
+Buffers may be numpy uint64 arrays (host memory; staged through the device by the library), torch CUDA tensors
+of dtype int64/uint64 (used in place) or raw integer addresses.
+"""
+import ctypes
+import pathlib
+
+import numpy as np
+
+__all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL",
+           "extend_and_merkelize", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
+
+GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
+_HERE = pathlib.Path(__file__).resolve().parent
+lib_path = _HERE / "libzkgpu.so"
+
+_u64 = ctypes.c_uint64
+_vp = ctypes.c_void_p
+_int = ctypes.c_int
+
+# every symbol include/zkgpu.h declares: (restype, argtypes)
+ABI_SYMBOLS = {
+    "zkgpu_init": (_int, [_int]),
+    "zkgpu_set_stream": (_int, [_vp]),
+    "zkgpu_sync": (_int, []),
+    "zkgpu_last_error": (ctypes.c_char_p, []),
+    "zkgpu_device_count": (_int, []),
+    "zkgpu_mem_info": (_int, [ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
+    "zkgpu_malloc": (_int, [ctypes.POINTER(_vp), _u64]),
+    "zkgpu_free": (_int, [_vp]),
+    "zkgpu_malloc_host": (_int, [ctypes.POINTER(_vp), _u64]),
+    "zkgpu_free_host": (_int, [_vp]),
+    "zkgpu_memcpy": (_int, [_vp, _vp, _u64]),
+    "zkgpu_stage_ms": (_int, [ctypes.POINTER(ctypes.c_float)]),
+    "zkgpu_fill": (_int, [_vp, _u64, _u64, _u64]),
+    "zkgpu_field_op": (_int, [_int, _vp, _vp, _vp, _u64]),
+    "zkgpu_ntt_create": (_vp, [_u64, _int]),
+    "zkgpu_ntt_destroy": (None, [_vp]),
+    "zkgpu_ntt": (_int, [_vp, _vp, _vp, _u64, _u64, _vp, _int, _int]),
+    "zkgpu_extend_pol": (_int, [_vp, _vp, _vp, _u64, _u64, _u64, _vp]),
+    "zkgpu_hash_full_result": (_int, [_vp, _vp, _u64]),
+    "zkgpu_linear_hash": (_int, [_vp, _vp, _u64]),
+    "zkgpu_merkletree": (_int, [_vp, _vp, _u64, _u64, _u64]),
+    "zkgpu_merkletree_batch": (_int, [_vp, _vp, _u64, _u64, _u64, _u64]),
+    "zkgpu_extend_and_merkelize": (_int, [_vp, _vp, _vp, _vp, _u64, _u64, _u64]),
+    "zkgpu_lde_columns": (_int, [_vp, _u64, _vp, _u64, _u64, _u64, _u64]),
+    "zkgpu_merkle_leaves": (_int, [_vp, _vp, _u64, _u64, _u64]),
+    "zkgpu_merkle_levels": (_int, [_vp, _u64]),
+    "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
+}
+
+
+class ZkGpuError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """The loaded libzkgpu.so (built by __graft_entry__.build() / make -C zkevm_prover_b200/csrc)."""
+    global _lib
+    if _lib is None:
+        if not lib_path.exists():
+            raise ZkGpuError("%s is missing: build it with `make -C zkevm_prover_b200/csrc` "
+                             "(there is no CPU fallback)" % lib_path)
+        L = ctypes.CDLL(str(lib_path))
+        for name, (res, args) in ABI_SYMBOLS.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc is not None and rc < 0:
+        raise ZkGpuError(lib().zkgpu_last_error().decode("utf-8", "replace"))
+
+
+def _ptr(x):
+    """Address of a numpy array / torch tensor / int / None."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if isinstance(x, np.ndarray):
+        if x.dtype != np.uint64 or not x.flags["C_CONTIGUOUS"]:
+            raise TypeError("host buffers must be C-contiguous numpy uint64 arrays")
+        return x.ctypes.data
+    if hasattr(x, "data_ptr"):  # torch tensor
+        if x.element_size() != 8 or not x.is_contiguous():
+            raise TypeError("device buffers must be contiguous 64-bit torch tensors")
+        return x.data_ptr()
+    raise TypeError("unsupported buffer type %r" % type(x))
+
+
+def init(device=-1):
+    _check(lib().zkgpu_init(device))
+
+
+def set_stream(stream=None):
+    """Enqueue on `stream` (a torch.cuda.Stream, a raw cudaStream_t integer, or None for the library's own)."""
+    h = None if stream is None else getattr(stream, "cuda_stream", stream)
+    _check(lib().zkgpu_set_stream(h))
+
+
+def sync():
+    _check(lib().zkgpu_sync())
+
+
+def stage_ms():
+    """{'lde', 'leaves', 'nodes', 'h2d', 'd2h'} device times in ms of the last commit-type call."""
+    out = (ctypes.c_float * 5)()
+    _check(lib().zkgpu_stage_ms(out))
+    return dict(zip(("lde", "leaves", "nodes", "h2d", "d2h"), [float(v) for v in out]))
+
+
+def fill(dst, n, seed=0x9E3779B97F4A7C15, offset=0):
+    """dst[i] = splitmix64(seed + offset + i) mod p — the synthetic trace generator shared with the oracle."""
+    _check(lib().zkgpu_fill(_ptr(dst), n, seed & (2**64 - 1), offset))
+
+
+def field_op(op, a, b):
+    """Element-wise device field arithmetic (KAT hook): op in {'add','sub','mul','mul_nc','canon'}."""
+    code = {"add": 0, "sub": 1, "mul": 2, "mul_nc": 3, "canon": 4}[op]
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    b = np.ascontiguousarray(b, dtype=np.uint64)
+    out = np.zeros_like(a)
+    _check(lib().zkgpu_field_op(code, _ptr(out), _ptr(a), _ptr(b), a.size))
+    return out
+
+
+class NTT_Goldilocks:
+    """Mirror of the reference class (src/goldilocks/src/ntt_goldilocks.hpp:49-173)."""
+
+    def __init__(self, maxDomainSize, nThreads=0, extension=1):
+        self._h = lib().zkgpu_ntt_create(maxDomainSize, extension)
+        if not self._h:
+            # the reference throws std::range_error("Domain size too big for the curve")
+            raise OverflowError(lib().zkgpu_last_error().decode())
+        self.maxDomainSize, self.nThreads, self.extension = maxDomainSize, nThreads, extension
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().zkgpu_ntt_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def NTT(self, dst, src, size, ncols=1, buffer=None, nphase=3, nblock=1, inverse=False, extend=False):
+        _check(lib().zkgpu_ntt(self._h, _ptr(dst), _ptr(src), size, ncols, _ptr(buffer), int(inverse), int(extend)))
+
+    def INTT(self, dst, src, size, ncols=1, buffer=None, nphase=3, nblock=1, extend=False):
+        _check(lib().zkgpu_ntt(self._h, _ptr(dst), _ptr(src), size, ncols, _ptr(buffer), 1, int(extend)))
+
+    def extendPol(self, output, input, N_Extended, N, ncols, buffer=None, nphase=3, nblock=1):
+        _check(lib().zkgpu_extend_pol(self._h, _ptr(output), _ptr(input), N_Extended, N, ncols, _ptr(buffer)))
+
+
+class PoseidonGoldilocks:
+    """Mirror of the reference's static class (src/goldilocks/src/poseidon_goldilocks.hpp:43-81)."""
+    RATE, CAPACITY, HASH_SIZE, SPONGE_WIDTH = 8, 4, 4, 12
+
+    @staticmethod
+    def hash_full_result(out, inp, n=1):
+        _check(lib().zkgpu_hash_full_result(_ptr(out), _ptr(inp), n))
+
+    @staticmethod
+    def hash(out4, inp12):
+        full = np.zeros(12, dtype=np.uint64)
+        PoseidonGoldilocks.hash_full_result(full, inp12)
+        out4[:4] = full[:4]
+
+    @staticmethod
+    def linear_hash(out4, inp, size):
+        _check(lib().zkgpu_linear_hash(_ptr(out4), _ptr(inp), size))
+
+    @staticmethod
+    def merkletree(tree, inp, num_cols, num_rows, nThreads=0, dim=1):
+        _check(lib().zkgpu_merkletree(_ptr(tree), _ptr(inp), num_cols, num_rows, dim))
+
+    merkletree_avx = merkletree
+    merkletree_seq = merkletree
+
+    @staticmethod
+    def merkletree_batch(tree, inp, num_cols, num_rows, batch_size, nThreads=0, dim=1):
+        _check(lib().zkgpu_merkletree_batch(_ptr(tree), _ptr(inp), num_cols, num_rows, batch_size, dim))
+
+
+class MerkleTreeGL:
+    """Mirror of src/starkpil/merkleTree/merkleTreeGL.hpp:9-79 / .cpp:5-44 for host (numpy) sources."""
+
+    def __init__(self, height, width, source=None):
+        self.height, self.width = height, width
+        self.source = source if source is not None else np.zeros(height * width, dtype=np.uint64)
+        self.nodes = np.zeros(self.getTreeNumElements(), dtype=np.uint64)
+
+    def getTreeNumElements(self):
+        # MerklehashGoldilocks::getTreeNumElements, merklehash_goldilocks.hpp:15-19
+        return self.height * 4 + (self.height - 1) * 4
+
+    def MerkleProofSize(self):
+        h, n = self.height, 0
+        while h > 1:
+            h >>= 1
+            n += 1
+        return n
+
+    def merkelize(self):
+        PoseidonGoldilocks.merkletree(self.nodes, self.source, self.width, self.height)
+
+    def getRoot(self):
+        return self.nodes[self.getTreeNumElements() - 4:].copy()
+
+    def getGroupProof(self, idx):
+        """merkleTreeGL.cpp:12-35: the source row followed by the sibling path (4 words per level)."""
+        src = np.asarray(self.source).reshape(self.height, self.width)
+        proof = [src[idx].copy()]
+        offset, n, i = 0, self.height, idx
+        while n > 1:
+            sib = i ^ 1
+            proof.append(self.nodes[offset + sib * 4: offset + sib * 4 + 4].copy())
+            offset += n * 4
+            n >>= 1
+            i >>= 1
+        return np.concatenate(proof)
+
+
+def extend_and_merkelize(ntt, out_ext, tree, inp, N_Extended, N, ncols):
+    """Starks::genProof commit stage k (starks.cpp:51-58): extendPol then MerkleTreeGL::merkelize, one call."""
+    _check(lib().zkgpu_extend_and_merkelize(ntt._h if ntt is not None else None, _ptr(out_ext), _ptr(tree), _ptr(inp),
+                                            N_Extended, N, ncols))

@@ -1,0 +1,671 @@
+// api.cu — the C ABI of libzkgpu.so (include/zkgpu.h): context, host/device pointer handling, staging,
+// stage timers, and the orchestration of the commit stage (LDE strips -> leaf hashing -> node levels).
+#include "gl64.cuh"
+#include "zk_internal.h"
+#include "../../include/zkgpu.h"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+namespace zk {
+
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+struct Ctx
+{
+    bool ready = false;
+    int device = 0;
+    cudaStream_t own = nullptr, cur = nullptr;
+    u64 *scratch = nullptr;
+    size_t scratch_words = 0;
+    cudaEvent_t ev[8] = {};
+    bool timed = false;
+    float stage[5] = {0, 0, 0, 0, 0};
+};
+static Ctx g_ctx;
+static std::recursive_mutex g_mu;
+
+static int ctx_init(int device)
+{
+    if (g_ctx.ready && (device < 0 || device == g_ctx.device)) return 0;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+    {
+        cudaGetLastError();
+        set_error("zkgpu: no usable CUDA device (%s); this library has no CPU fallback",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return -3;
+    }
+    if (device >= 0) ZK_CUDA(cudaSetDevice(device));
+    ZK_CUDA(cudaGetDevice(&g_ctx.device));
+    cudaDeviceProp prop;
+    ZK_CUDA(cudaGetDeviceProperties(&prop, g_ctx.device));
+    if (prop.major < 10)
+    {
+        set_error("zkgpu: device %d is sm_%d%d; this build contains sm_100a code only", g_ctx.device, prop.major, prop.minor);
+        return -3;
+    }
+    if (!g_ctx.own) ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.own, cudaStreamNonBlocking));
+    if (!g_ctx.cur) g_ctx.cur = g_ctx.own;
+    for (auto &ev : g_ctx.ev)
+        if (!ev) ZK_CUDA(cudaEventCreate(&ev));
+    g_ctx.ready = true;
+    ZK_TRY(poseidon_init_constants());
+    return 0;
+}
+
+static int ensure_scratch(size_t words)
+{
+    if (words <= g_ctx.scratch_words) return 0;
+    if (g_ctx.scratch)
+    {
+        ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+        ZK_CUDA(cudaFree(g_ctx.scratch));
+        g_ctx.scratch = nullptr;
+        g_ctx.scratch_words = 0;
+    }
+    ZK_CUDA(cudaMalloc(&g_ctx.scratch, words * sizeof(u64)));
+    g_ctx.scratch_words = words;
+    return 0;
+}
+
+static bool is_device_ptr(const void *p)
+{
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+static inline bool is_pow2(u64 x) { return x && !(x & (x - 1)); }
+static inline unsigned ilog2(u64 x)
+{
+    unsigned r = 0;
+    while (x > 1)
+    {
+        x >>= 1;
+        r++;
+    }
+    return r;
+}
+
+// ---- small kernels ----
+__device__ __forceinline__ u64 splitmix64(u64 x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__global__ void fill_kernel(u64 *dst, u64 n, u64 seed, u64 offset)
+{
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+        dst[i] = splitmix64(seed + offset + i) % GL_P;
+}
+int fill_splitmix(u64 *dst, u64 n, u64 seed, u64 offset, cudaStream_t st)
+{
+    if (n == 0) return 0;
+    u64 blocks = (n + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    fill_kernel<<<(unsigned)blocks, 256, 0, st>>>(dst, n, seed, offset);
+    ZK_CUDA(cudaGetLastError());
+    return 0;
+}
+__global__ void copy_block_kernel(u64 *dst, u64 dst_ld, const u64 *src, u64 src_ld, u64 nrows, u64 ncols)
+{
+    const u64 total = nrows * ncols;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (u64)gridDim.x * blockDim.x)
+    {
+        const u64 r = i / ncols, c = i - r * ncols;
+        dst[r * dst_ld + c] = src[r * src_ld + c];
+    }
+}
+
+__global__ void field_op_kernel(int op, u64 *out, const u64 *a, const u64 *b, u64 n)
+{
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+    {
+        const u64 x = a[i], y = b[i];
+        u64 r;
+        switch (op)
+        {
+        case 0: r = gl::canon(gl::add(x, gl::canon(y))); break; // gl::add needs one operand < p
+        case 1: r = gl::canon(gl::sub(x, gl::canon(y))); break;
+        case 2: r = gl::mul(x, y); break;
+        case 3: r = gl::canon(gl::mul_nc(x, y)); break;
+        default: r = gl::canon(x); break;
+        }
+        out[i] = r;
+    }
+}
+
+// ---- LDE over all columns in strips that fit the scratch budget ----
+static int lde_all(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, unsigned log_n, unsigned log_b, u64 ncols, cudaStream_t st)
+{
+    if (ncols == 0) return 0;
+    const u64 n = (u64)1 << log_n;
+    size_t free_b = 0, total_b = 0;
+    ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    free_b += g_ctx.scratch_words * sizeof(u64);
+    size_t budget = (size_t)(0.6 * (double)free_b);
+    const size_t cap = (size_t)16 << 30;
+    if (budget > cap) budget = cap;
+    u64 w = budget / (2 * n * sizeof(u64));
+    if (w >= ncols)
+        w = ncols;
+    else
+    {
+        w &= ~(u64)15;
+        if (w == 0)
+        {
+            set_error("extendPol: not enough device memory for a 16-column strip of 2^%u rows", log_n);
+            return -4;
+        }
+    }
+    ZK_TRY(ensure_scratch(2 * n * w));
+    for (u64 c0 = 0; c0 < ncols; c0 += w)
+    {
+        const u64 cw = ncols - c0 < w ? ncols - c0 : w;
+        ZK_TRY(lde_strip(out + c0, out_ld, in + c0, in_ld, g_ctx.scratch, log_n, log_b, cw, st));
+    }
+    return 0;
+}
+
+static int merkle_all(u64 *tree, const u64 *input, u64 row_words, u64 nrows, cudaStream_t st, cudaEvent_t mid)
+{
+    ZK_TRY(merkle_leaves(tree, input, row_words, row_words, nrows, st));
+    if (mid) ZK_CUDA(cudaEventRecord(mid, st));
+    ZK_TRY(merkle_levels(tree, nrows, st));
+    return 0;
+}
+
+// staging helper: device mirror of a host buffer
+struct Staged
+{
+    u64 *d = nullptr;
+    bool owned = false;
+    ~Staged()
+    {
+        if (owned && d) cudaFree(d);
+    }
+    int alloc(u64 words)
+    {
+        if (words == 0) words = 1;
+        cudaError_t e = cudaMalloc(&d, words * sizeof(u64));
+        if (e != cudaSuccess)
+        {
+            cudaGetLastError();
+            set_error("zkgpu: cannot stage %llu MiB on the device (%s)", (unsigned long long)(words >> 17), cudaGetErrorString(e));
+            return -4;
+        }
+        owned = true;
+        return 0;
+    }
+};
+
+} // namespace zk
+
+using namespace zk;
+#define LOCK std::lock_guard<std::recursive_mutex> lk__(g_mu)
+#define NEED_CTX ZK_TRY(ctx_init(-1))
+
+extern "C" {
+
+int zkgpu_init(int device)
+{
+    LOCK;
+    return ctx_init(device);
+}
+int zkgpu_set_stream(void *s)
+{
+    LOCK;
+    NEED_CTX;
+    g_ctx.cur = s ? (cudaStream_t)s : g_ctx.own;
+    return 0;
+}
+int zkgpu_sync(void)
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    return 0;
+}
+const char *zkgpu_last_error(void) { return g_err; }
+int zkgpu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes)
+{
+    LOCK;
+    NEED_CTX;
+    size_t f = 0, t = 0;
+    ZK_CUDA(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+    return 0;
+}
+int zkgpu_malloc(void **p, uint64_t bytes)
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaMalloc(p, bytes ? bytes : 8));
+    return 0;
+}
+int zkgpu_free(void *p)
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    ZK_CUDA(cudaFree(p));
+    return 0;
+}
+int zkgpu_malloc_host(void **p, uint64_t bytes)
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaMallocHost(p, bytes ? bytes : 8));
+    return 0;
+}
+int zkgpu_free_host(void *p)
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaFreeHost(p));
+    return 0;
+}
+int zkgpu_memcpy(void *dst, const void *src, uint64_t bytes)
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, g_ctx.cur));
+    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    return 0;
+}
+int zkgpu_stage_ms(float out[5])
+{
+    LOCK;
+    NEED_CTX;
+    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    if (g_ctx.timed)
+    {
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[0], g_ctx.ev[0], g_ctx.ev[1]));
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[1], g_ctx.ev[1], g_ctx.ev[2]));
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[2], g_ctx.ev[2], g_ctx.ev[3]));
+        g_ctx.timed = false;
+    }
+    for (int i = 0; i < 5; i++) out[i] = g_ctx.stage[i];
+    return 0;
+}
+int zkgpu_fill(uint64_t *dst, uint64_t n, uint64_t seed, uint64_t offset)
+{
+    LOCK;
+    NEED_CTX;
+    if (is_device_ptr(dst)) return fill_splitmix(dst, n, seed, offset, g_ctx.cur);
+    Staged d;
+    ZK_TRY(d.alloc(n));
+    ZK_TRY(fill_splitmix(d.d, n, seed, offset, g_ctx.cur));
+    ZK_CUDA(cudaMemcpyAsync(dst, d.d, n * sizeof(u64), cudaMemcpyDeviceToHost, g_ctx.cur));
+    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    return 0;
+}
+
+int zkgpu_field_op(int op, uint64_t *out, const uint64_t *a, const uint64_t *b, uint64_t n)
+{
+    LOCK;
+    if (n == 0) return 0;
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const bool dev = is_device_ptr(out);
+    Staged da, db;
+    const u64 *pa = a, *pb = b;
+    u64 *po = out;
+    if (!dev)
+    {
+        ZK_TRY(da.alloc(n));
+        ZK_TRY(db.alloc(n));
+        ZK_CUDA(cudaMemcpyAsync(da.d, a, n * sizeof(u64), cudaMemcpyHostToDevice, st));
+        ZK_CUDA(cudaMemcpyAsync(db.d, b, n * sizeof(u64), cudaMemcpyHostToDevice, st));
+        pa = da.d;
+        pb = db.d;
+        po = da.d;
+    }
+    u64 blocks = (n + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    field_op_kernel<<<(unsigned)blocks, 256, 0, st>>>(op, po, pa, pb, n);
+    ZK_CUDA(cudaGetLastError());
+    if (!dev)
+    {
+        ZK_CUDA(cudaMemcpyAsync(out, po, n * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaStreamSynchronize(st));
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+struct NttHandle
+{
+    u64 max_domain;
+    int extension;
+};
+void *zkgpu_ntt_create(uint64_t max_domain_size, int extension)
+{
+    if (max_domain_size && ilog2(max_domain_size) > 32)
+    {
+        set_error("Domain size too big for the curve"); // ntt_goldilocks.hpp:94-97
+        return nullptr;
+    }
+    return new NttHandle{max_domain_size, extension};
+}
+void zkgpu_ntt_destroy(void *h) { delete (NttHandle *)h; }
+
+int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, uint64_t *, int inverse, int extend)
+{
+    LOCK;
+    if (size == 0 || ncols == 0) return 0; // ntt_goldilocks.cpp:168-171
+    if (!is_pow2(size))
+    {
+        set_error("NTT: size %llu is not a power of two", (unsigned long long)size); // reference asserts
+        return -1;
+    }
+    if (!src)
+    {
+        set_error("NTT: src is NULL");
+        return -1;
+    }
+    NEED_CTX;
+    if (!dst) dst = const_cast<uint64_t *>(src);
+    const unsigned L = ilog2(size);
+    cudaStream_t st = g_ctx.cur;
+    Scale pre, post;
+    if (inverse)
+    {
+        const u64 ninv = gl::pow_slow(size % GL_P, GL_P - 2);
+        if (extend)
+        {
+            post.mode = SCALE_POWER;
+            ZK_TRY(get_power_tables(GL_SHIFT, ninv, L, &post.G0, &post.G1, st));
+        }
+        else if (size > 1)
+        {
+            post.mode = SCALE_CONST;
+            post.konst = ninv;
+        }
+    }
+    const bool dev = is_device_ptr(src);
+    if (dev != is_device_ptr(dst))
+    {
+        set_error("NTT: dst and src must both be host or both be device pointers");
+        return -1;
+    }
+    const u64 words = size * ncols;
+    if (dev)
+    {
+        if (L > 8) ZK_TRY(ensure_scratch(words));
+        return ntt_transform(dst, ncols, src, ncols, g_ctx.scratch, L, ncols, inverse != 0, pre, post, st);
+    }
+    Staged d;
+    ZK_TRY(d.alloc(words));
+    if (L > 8) ZK_TRY(ensure_scratch(words));
+    ZK_CUDA(cudaMemcpyAsync(d.d, src, words * sizeof(u64), cudaMemcpyHostToDevice, st));
+    ZK_TRY(ntt_transform(d.d, ncols, d.d, ncols, g_ctx.scratch, L, ncols, inverse != 0, pre, post, st));
+    ZK_CUDA(cudaMemcpyAsync(dst, d.d, words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+static int check_lde_args(uint64_t n_ext, uint64_t n, unsigned *log_n, unsigned *log_b)
+{
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n)
+    {
+        set_error("extendPol: N=%llu, N_Extended=%llu must be powers of two with N_Extended >= N", (unsigned long long)n,
+                  (unsigned long long)n_ext);
+        return -1;
+    }
+    *log_n = ilog2(n);
+    *log_b = ilog2(n_ext) - *log_n;
+    return 0;
+}
+
+int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64_t in_ld, uint64_t n_ext, uint64_t n,
+                      uint64_t ncols)
+{
+    LOCK;
+    if (n == 0 || ncols == 0) return 0;
+    unsigned log_n, log_b;
+    ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
+    NEED_CTX;
+    if (!is_device_ptr(out) || !is_device_ptr(in))
+    {
+        set_error("zkgpu_lde_columns: device pointers required");
+        return -1;
+    }
+    return lde_all(out, out_ld, in, in_ld, log_n, log_b, ncols, g_ctx.cur);
+}
+
+int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n_ext, uint64_t n, uint64_t ncols, uint64_t *)
+{
+    LOCK;
+    if (n == 0 || ncols == 0 || n_ext == 0) return 0;
+    unsigned log_n, log_b;
+    ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const bool dev = is_device_ptr(input);
+    if (dev != is_device_ptr(output))
+    {
+        set_error("extendPol: output and input must both be host or both be device pointers");
+        return -1;
+    }
+    if (dev)
+    {
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
+        ZK_TRY(lde_all(output, ncols, input, ncols, log_n, log_b, ncols, st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+        g_ctx.timed = true;
+        return 0;
+    }
+    Staged din, dout;
+    ZK_TRY(din.alloc(n * ncols));
+    ZK_TRY(dout.alloc(n_ext * ncols));
+    ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
+    ZK_TRY(lde_all(dout.d, ncols, din.d, ncols, log_n, log_b, ncols, st));
+    ZK_CUDA(cudaMemcpyAsync(output, dout.d, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+int zkgpu_hash_full_result(uint64_t *out12, const uint64_t *in12, uint64_t n)
+{
+    LOCK;
+    if (n == 0) return 0;
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    if (is_device_ptr(in12)) return poseidon_permute(out12, in12, n, st);
+    Staged d;
+    ZK_TRY(d.alloc(12 * n));
+    ZK_CUDA(cudaMemcpyAsync(d.d, in12, 12 * n * sizeof(u64), cudaMemcpyHostToDevice, st));
+    ZK_TRY(poseidon_permute(d.d, d.d, n, st));
+    ZK_CUDA(cudaMemcpyAsync(out12, d.d, 12 * n * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int zkgpu_linear_hash(uint64_t *out4, const uint64_t *input, uint64_t size)
+{
+    LOCK;
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    if (is_device_ptr(input)) return merkle_leaves(out4, input, size, size, 1, st);
+    Staged d;
+    ZK_TRY(d.alloc(size + 4));
+    if (size) ZK_CUDA(cudaMemcpyAsync(d.d + 4, input, size * sizeof(u64), cudaMemcpyHostToDevice, st));
+    ZK_TRY(merkle_leaves(d.d, d.d + 4, size, size, 1, st));
+    ZK_CUDA(cudaMemcpyAsync(out4, d.d, 4 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+static int merkletree_impl(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t batch, uint64_t dim,
+                           bool batched)
+{
+    if (nrows == 0) return 0; // poseidon_goldilocks.cpp:268-271
+    if (!is_pow2(nrows))
+    {
+        set_error("merkletree: num_rows %llu is not a power of two", (unsigned long long)nrows);
+        return -1;
+    }
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const u64 row_words = ncols * dim;
+    const u64 tree_words = (2 * nrows - 1) * 4;
+    const bool dev = is_device_ptr(tree);
+    if (row_words && dev != is_device_ptr(input))
+    {
+        set_error("merkletree: tree and input must both be host or both be device pointers");
+        return -1;
+    }
+    Staged din, dtree;
+    const u64 *d_in = input;
+    u64 *d_tree = tree;
+    if (!dev)
+    {
+        ZK_TRY(din.alloc(nrows * row_words));
+        ZK_TRY(dtree.alloc(tree_words));
+        if (row_words) ZK_CUDA(cudaMemcpyAsync(din.d, input, nrows * row_words * sizeof(u64), cudaMemcpyHostToDevice, st));
+        d_in = din.d;
+        d_tree = dtree.d;
+    }
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
+    if (batched)
+    {
+        ZK_TRY(merkle_leaves_batch(d_tree, d_in, ncols, dim, batch, nrows, st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+        ZK_TRY(merkle_levels(d_tree, nrows, st));
+    }
+    else
+        ZK_TRY(merkle_all(d_tree, d_in, row_words, nrows, st, g_ctx.ev[2]));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+    g_ctx.timed = true;
+    if (!dev)
+    {
+        ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaStreamSynchronize(st));
+    }
+    return 0;
+}
+int zkgpu_merkletree(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t dim)
+{
+    LOCK;
+    return merkletree_impl(tree, input, ncols, nrows, 0, dim, false);
+}
+int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t batch, uint64_t dim)
+{
+    LOCK;
+    return merkletree_impl(tree, input, ncols, nrows, batch, dim, true);
+}
+
+int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_words, uint64_t row_ld, uint64_t nrows)
+{
+    LOCK;
+    NEED_CTX;
+    return merkle_leaves(leaves, rows, row_words, row_ld, nrows, g_ctx.cur);
+}
+int zkgpu_merkle_levels(uint64_t *tree, uint64_t nrows)
+{
+    LOCK;
+    if (nrows == 0) return 0;
+    if (!is_pow2(nrows))
+    {
+        set_error("merkle_levels: num_rows %llu is not a power of two", (unsigned long long)nrows);
+        return -1;
+    }
+    NEED_CTX;
+    return merkle_levels(tree, nrows, g_ctx.cur);
+}
+int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64_t src_ld, uint64_t nrows, uint64_t ncols)
+{
+    LOCK;
+    NEED_CTX;
+    const u64 total = nrows * ncols;
+    if (total == 0) return 0;
+    u64 blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    copy_block_kernel<<<(unsigned)blocks, 256, 0, g_ctx.cur>>>(dst, dst_ld, src, src_ld, nrows, ncols);
+    ZK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const uint64_t *input, uint64_t n_ext, uint64_t n,
+                               uint64_t ncols)
+{
+    LOCK;
+    if (n == 0 || n_ext == 0) return 0;
+    unsigned log_n, log_b;
+    ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const bool dev = is_device_ptr(tree);
+    if (ncols && (dev != is_device_ptr(input) || dev != is_device_ptr(out_ext)))
+    {
+        set_error("extend_and_merkelize: all pointers must be host or all device");
+        return -1;
+    }
+    const u64 tree_words = (2 * n_ext - 1) * 4;
+    Staged din, dout, dtree;
+    const u64 *d_in = input;
+    u64 *d_out = out_ext, *d_tree = tree;
+    if (!dev)
+    {
+        ZK_TRY(din.alloc(n * ncols));
+        ZK_TRY(dout.alloc(n_ext * ncols));
+        ZK_TRY(dtree.alloc(tree_words));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[4], st));
+        if (ncols) ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
+        d_in = din.d;
+        d_out = dout.d;
+        d_tree = dtree.d;
+    }
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
+    ZK_TRY(lde_all(d_out, ncols, d_in, ncols, log_n, log_b, ncols, st));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
+    ZK_TRY(merkle_all(d_tree, d_out, ncols, n_ext, st, g_ctx.ev[2]));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+    g_ctx.timed = true;
+    if (!dev)
+    {
+        if (ncols) ZK_CUDA(cudaMemcpyAsync(out_ext, d_out, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[5], st));
+        ZK_CUDA(cudaStreamSynchronize(st));
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[3], g_ctx.ev[4], g_ctx.ev[0]));
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[4], g_ctx.ev[3], g_ctx.ev[5]));
+    }
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,153 @@
+// gl64.cuh — Goldilocks field (p = 2^64 - 2^32 + 1) device arithmetic for sm_100a.
+//
+// Replaces the reference's x86 inline-asm scalar ops (src/goldilocks/src/goldilocks_base_field_scalar.hpp:
+// add :16-35, sub :62-80, mul :103-160) and Goldilocks::toU64 (goldilocks_base_field_tools.hpp:152-163).
+// The reference leaves words un-normalised in [0, 2^64); every consumer compares through toU64.  Here:
+//   * gl_mul      -> canonical word (< p)
+//   * gl_mul_nc   -> word in [0, 2^64) congruent to a*b (two instructions cheaper; for mul-only chains)
+//   * gl_add(a,b) -> requires b < p  (or a < p); result in [0, 2^64)
+//   * gl_sub(a,b) -> requires b <= p;            result in [0, 2^64)
+//   * gl_canon    -> toU64
+// Everything the library stores to caller-visible memory is canonical.
+//
+// Built from 32-bit IMAD.WIDE / IADD3 carry chains (there is no 64-bit integer multiplier on the SM):
+// product = 4 IMAD.WIDE.U32 + 3 carry ops, reduction uses 2^64 = 2^32 - 1 and 2^96 = -1 (mod p).
+#pragma once
+#include <cstdint>
+
+typedef uint64_t u64;
+typedef uint32_t u32;
+
+#define GL_P 0xFFFFFFFF00000001ull
+#define GL_EPS 0xFFFFFFFFu
+
+namespace gl {
+
+__host__ __device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi << 32) | lo; }
+
+#ifdef __CUDACC__
+#define GL_DEV __device__ __forceinline__
+
+// x = (r1:r0) + r2*(2^32-1) - r3  folded into [0, 2^64).   [hi word = r3:r2]
+// CANON: additionally x < p.
+template <bool CANON>
+GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
+{
+    u32 x0, x1;
+    if (CANON)
+    {
+        asm("{\n\t.reg .u32 m, c, u0, u1;\n\t.reg .pred q;\n\t"
+            "sub.cc.u32 %0, %2, %5;\n\t"   // t = lo - r3
+            "subc.cc.u32 %1, %3, 0;\n\t"
+            "subc.u32 m, 0, 0;\n\t"        // m = borrow ? 0xFFFFFFFF : 0
+            "sub.cc.u32 %0, %0, m;\n\t"    // t -= eps  (lo + 1, hi - 1 + carry)  when borrow
+            "addc.u32 %1, %1, m;\n\t"
+            "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t" // r = t + r2*eps
+            "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
+            "addc.u32 c, 0, 0;\n\t"        // c = carry out of r
+            "add.cc.u32 u0, %0, 0xFFFFFFFF;\n\t" // u = r + eps = r - p (mod 2^64)
+            "addc.cc.u32 u1, %1, 0;\n\t"
+            "addc.u32 c, c, 0;\n\t"        // c != 0  <=>  carry (r wrapped) or r >= p
+            "setp.ne.u32 q, c, 0;\n\t"
+            "selp.u32 %0, u0, %0, q;\n\t"
+            "selp.u32 %1, u1, %1, q;\n\t}"
+            : "=&r"(x0), "=&r"(x1)
+            : "r"(r0), "r"(r1), "r"(r2), "r"(r3));
+    }
+    else
+    {
+        asm("{\n\t.reg .u32 m, c;\n\t"
+            "sub.cc.u32 %0, %2, %5;\n\t"
+            "subc.cc.u32 %1, %3, 0;\n\t"
+            "subc.u32 m, 0, 0;\n\t"
+            "sub.cc.u32 %0, %0, m;\n\t"
+            "addc.u32 %1, %1, m;\n\t"
+            "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t"
+            "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
+            "addc.u32 c, 0, 0;\n\t"
+            "sub.u32 c, 0, c;\n\t"         // mask
+            "add.cc.u32 %0, %0, c;\n\t"    // r += eps when carry
+            "addc.u32 %1, %1, 0;\n\t}"
+            : "=&r"(x0), "=&r"(x1)
+            : "r"(r0), "r"(r1), "r"(r2), "r"(r3));
+    }
+    return pack(x0, x1);
+}
+
+template <bool CANON>
+GL_DEV u64 mul_t(u64 a, u64 b)
+{
+    unsigned __int128 pr = (unsigned __int128)a * b;
+    u64 lo = (u64)pr, hi = (u64)(pr >> 64);
+    return reduce128<CANON>((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
+}
+GL_DEV u64 mul(u64 a, u64 b) { return mul_t<true>(a, b); }
+GL_DEV u64 mul_nc(u64 a, u64 b) { return mul_t<false>(a, b); }
+GL_DEV u64 sqr_nc(u64 a) { return mul_t<false>(a, a); }
+
+// a + b, requires min(a,b) < p (then a single 2^64 -> eps fold cannot overflow again)
+GL_DEV u64 add(u64 a, u64 b)
+{
+    u32 s0, s1;
+    asm("{\n\t.reg .u32 c;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\t"
+        "addc.cc.u32 %1, %3, %5;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "sub.u32 c, 0, c;\n\t"
+        "add.cc.u32 %0, %0, c;\n\t"
+        "addc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(s0), "=&r"(s1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    return pack(s0, s1);
+}
+// a - b, requires b <= p
+GL_DEV u64 sub(u64 a, u64 b)
+{
+    u32 s0, s1;
+    asm("{\n\t.reg .u32 m;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, %3, %5;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\t"
+        "addc.u32 %1, %1, m;\n\t}"
+        : "=&r"(s0), "=&r"(s1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    return pack(s0, s1);
+}
+GL_DEV u64 canon(u64 x) { return x >= GL_P ? x - GL_P : x; }
+// -x for canonical x
+GL_DEV u64 neg(u64 x) { return x ? GL_P - x : 0; }
+
+#undef GL_DEV
+#endif // __CUDACC__
+
+// ---- host/device constexpr-ish helpers (table building, host-side constants) ----
+__host__ __device__ inline u64 mul_slow(u64 a, u64 b)
+{
+    unsigned __int128 pr = (unsigned __int128)a * b;
+    return (u64)(pr % GL_P);
+}
+__host__ __device__ inline u64 pow_slow(u64 b, u64 e)
+{
+    u64 r = 1;
+    b %= GL_P;
+    while (e)
+    {
+        if (e & 1) r = mul_slow(r, b);
+        b = mul_slow(b, b);
+        e >>= 1;
+    }
+    return r;
+}
+// primitive 2^32-th root of unity of the reference's table: Goldilocks::W[32]
+// (src/goldilocks/src/goldilocks_base_field.cpp:11-44); W[k] = W32^(2^(32-k)).
+#define GL_W32 7277203076849721926ull
+#define GL_SHIFT 7ull // Goldilocks::SHIFT, goldilocks_base_field.cpp:9 (coset generator)
+__host__ __device__ inline u64 root_of_unity(unsigned log2n)
+{
+    u64 w = GL_W32;
+    for (unsigned i = 32; i > log2n; --i) w = mul_slow(w, w);
+    return w;
+}
+
+} // namespace gl

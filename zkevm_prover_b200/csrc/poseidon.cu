@@ -1,0 +1,375 @@
+// poseidon.cu — Poseidon-Goldilocks permutation, row sponge (linear_hash) and Merkle tree kernels (sm_100a).
+//
+// Replaces PoseidonGoldilocks::{hash_full_result, linear_hash, merkletree_avx, merkletree_batch_avx}
+// (reference src/goldilocks/src/poseidon_goldilocks.cpp:166-228, 229-265, 266-301, 302-352; scalar statement of
+// the same math :5-112) and the AVX2 field helpers they use (goldilocks_base_field_avx.hpp:176-573).
+//
+// One thread owns one 12-word state in registers.  The round structure is the reference's "optimised"
+// Poseidon (4 full + 22 sparse partial + 4 full rounds, x^7), evaluated with GPU-shaped arithmetic:
+//   * S-box: 4 un-normalised multiplies (gl::mul_nc), operands may be any 64-bit word;
+//   * full-round MDS (entries <= 41): the state is split in 32-bit halves, each output is two 64-bit
+//     IMAD.WIDE accumulators (sum of M*lo, sum of M*hi) recombined and folded once (2^64 = 2^32-1);
+//   * dense P matrix and sparse-round dot products: 128-bit products accumulated in a 160-bit carry chain,
+//     folded once per output;
+//   * sparse-round column update st[i] += s0*S[i]: product and addend folded together.
+// Constants live in __constant__ memory (every thread of a warp reads the same word: broadcast).
+#include "gl64.cuh"
+#include "zk_internal.h"
+#include "poseidon_constants.inc"
+
+namespace zk {
+
+__constant__ u64 c_C[118];
+__constant__ u64 c_P[144];
+__constant__ u64 c_S[507];
+
+// MDS as the reference applies it: new[i] = sum_j M[j][i] * old[j]  (poseidon_goldilocks.hpp:148-162).
+// M is circulant: M[j][i] = circ[(i - j) mod 12] plus 8 on M[0][0].
+__device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
+{
+    constexpr u32 row0[12] = {17, 20, 34, 18, 39, 13, 13, 28, 2, 16, 41, 15}; // M[0][i] (without the +8 at [0][0])
+    return row0[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
+}
+
+__device__ __forceinline__ u64 pow7(u64 x)
+{
+    u64 x2 = gl::sqr_nc(x);
+    u64 x3 = gl::mul_nc(x, x2);
+    u64 x4 = gl::sqr_nc(x2);
+    return gl::mul_nc(x3, x4);
+}
+
+// x = lo64 + top * 2^64 with top < 2^32  ->  [0, 2^64)
+__device__ __forceinline__ u64 fold96(u32 r0, u32 r1, u32 r2)
+{
+    u32 x0, x1;
+    asm("{\n\t.reg .u32 c;\n\t"
+        "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %2;\n\t"
+        "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %3;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "sub.u32 c, 0, c;\n\t"
+        "add.cc.u32 %0, %0, c;\n\t"
+        "addc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(x0), "=&r"(x1)
+        : "r"(r0), "r"(r1), "r"(r2));
+    return gl::pack(x0, x1);
+}
+
+// st <- M^T-style product of the reference's mvp_ with the small MDS
+__device__ __forceinline__ void mds_small(u64 (&st)[12])
+{
+    u32 lo[12], hi[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++)
+    {
+        lo[j] = (u32)st[j];
+        hi[j] = (u32)(st[j] >> 32);
+    }
+#pragma unroll
+    for (int i = 0; i < 12; i++)
+    {
+        u64 al = 0, ah = 0;
+#pragma unroll
+        for (int j = 0; j < 12; j++)
+        {
+            al += (u64)lo[j] * mds_entry(j, i);
+            ah += (u64)hi[j] * mds_entry(j, i);
+        }
+        // value = al + ah * 2^32  (al, ah < 2^41)
+        u64 mid = (al >> 32) + (ah & 0xFFFFFFFFull); // < 2^33
+        u32 r0 = (u32)al;
+        u32 r1 = (u32)mid;
+        u32 r2 = (u32)(ah >> 32) + (u32)(mid >> 32);
+        st[i] = fold96(r0, r1, r2);
+    }
+}
+
+// 160-bit accumulator for sums of <= 2^32 products of 64-bit words
+struct Acc160
+{
+    u32 w0, w1, w2, w3, w4;
+    __device__ __forceinline__ void zero() { w0 = w1 = w2 = w3 = w4 = 0; }
+    __device__ __forceinline__ void mac(u64 a, u64 b)
+    {
+        unsigned __int128 pr = (unsigned __int128)a * b;
+        u64 l = (u64)pr, h = (u64)(pr >> 64);
+        asm("add.cc.u32 %0, %0, %5;\n\t"
+            "addc.cc.u32 %1, %1, %6;\n\t"
+            "addc.cc.u32 %2, %2, %7;\n\t"
+            "addc.cc.u32 %3, %3, %8;\n\t"
+            "addc.u32 %4, %4, 0;"
+            : "+r"(w0), "+r"(w1), "+r"(w2), "+r"(w3), "+r"(w4)
+            : "r"((u32)l), "r"((u32)(l >> 32)), "r"((u32)h), "r"((u32)(h >> 32)));
+    }
+    __device__ __forceinline__ void add64(u64 a)
+    {
+        asm("add.cc.u32 %0, %0, %5;\n\t"
+            "addc.cc.u32 %1, %1, %6;\n\t"
+            "addc.cc.u32 %2, %2, 0;\n\t"
+            "addc.cc.u32 %3, %3, 0;\n\t"
+            "addc.u32 %4, %4, 0;"
+            : "+r"(w0), "+r"(w1), "+r"(w2), "+r"(w3), "+r"(w4)
+            : "r"((u32)a), "r"((u32)(a >> 32)));
+    }
+    // value = W + w4 * 2^128, 2^128 = -2^32 (mod p).  w4 is tiny (< number of terms).
+    __device__ __forceinline__ u64 fold() const
+    {
+        u64 x = gl::reduce128<false>(w0, w1, w2, w3);         // [0, 2^64)
+        u64 y = (u64)w4 << 32;                                  // < p (w4 < 2^31)
+        return gl::sub(x, y);
+    }
+};
+
+// a*b + c folded to [0, 2^64)   (a*b + c < 2^128)
+__device__ __forceinline__ u64 mul_add_nc(u64 a, u64 b, u64 c)
+{
+    unsigned __int128 pr = (unsigned __int128)a * b + c;
+    u64 l = (u64)pr, h = (u64)(pr >> 64);
+    return gl::reduce128<false>((u32)l, (u32)(l >> 32), (u32)h, (u32)(h >> 32));
+}
+
+// The reference's hash_full_result on one state (poseidon_goldilocks.cpp:5-37 is the scalar statement).
+// Input words may be any 64-bit value; output words are in [0, 2^64) (callers canonicalise what they store).
+__device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
+{
+#pragma unroll
+    for (int i = 0; i < 12; i++) st[i] = gl::add(st[i], c_C[i]);
+#pragma unroll 1
+    for (int r = 0; r < 3; r++)
+    {
+#pragma unroll
+        for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), c_C[(r + 1) * 12 + i]);
+        mds_small(st);
+    }
+#pragma unroll
+    for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), c_C[48 + i]);
+    {
+        // dense P: new[i] = sum_j P[j][i] * old[j]
+        u64 nw[12];
+#pragma unroll
+        for (int i = 0; i < 12; i++)
+        {
+            Acc160 acc;
+            acc.zero();
+#pragma unroll
+            for (int j = 0; j < 12; j++) acc.mac(st[j], c_P[j * 12 + i]);
+            nw[i] = acc.fold();
+        }
+#pragma unroll
+        for (int i = 0; i < 12; i++) st[i] = nw[i];
+    }
+#pragma unroll 1
+    for (int r = 0; r < 22; r++)
+    {
+        const u64 *S = c_S + 23 * r;
+        const u64 s0 = gl::add(pow7(st[0]), c_C[60 + r]);
+        Acc160 acc;
+        acc.zero();
+        acc.mac(s0, S[0]);
+#pragma unroll
+        for (int i = 1; i < 12; i++) acc.mac(st[i], S[i]);
+#pragma unroll
+        for (int i = 1; i < 12; i++) st[i] = mul_add_nc(s0, S[11 + i], st[i]);
+        st[0] = acc.fold();
+    }
+#pragma unroll 1
+    for (int r = 0; r < 3; r++)
+    {
+#pragma unroll
+        for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), c_C[82 + r * 12 + i]);
+        mds_small(st);
+    }
+#pragma unroll
+    for (int i = 0; i < 12; i++) st[i] = pow7(st[i]);
+    mds_small(st);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) permute_kernel(u64 *out, const u64 *in, u64 n)
+{
+    const u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    u64 st[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) st[i] = in[t * 12 + i];
+    poseidon_permute_state(st);
+#pragma unroll
+    for (int i = 0; i < 12; i++) out[t * 12 + i] = gl::canon(st[i]);
+}
+
+// linear_hash of `count` words at p into out[0..3] (canonical).  poseidon_goldilocks.cpp:229-265:
+// count <= 4 is copied (zero padded) and NOT hashed; otherwise sponge with rate 8, capacity = previous out[0..3].
+__device__ __forceinline__ void linear_hash_words(u64 (&out)[4], const u64 *__restrict__ p, u64 count)
+{
+    if (count <= 4)
+    {
+#pragma unroll
+        for (int i = 0; i < 4; i++) out[i] = (u64)i < count ? gl::canon(p[i]) : 0;
+        return;
+    }
+    u64 st[12];
+#pragma unroll
+    for (int i = 8; i < 12; i++) st[i] = 0;
+    u64 done = 0;
+    while (done < count)
+    {
+        const u64 n = count - done < 8 ? count - done : 8;
+        if (n == 8)
+        {
+#pragma unroll
+            for (int i = 0; i < 8; i++) st[i] = p[done + i];
+        }
+        else
+        {
+#pragma unroll
+            for (int i = 0; i < 8; i++) st[i] = (u64)i < n ? p[done + i] : 0;
+        }
+        poseidon_permute_state(st);
+        done += n;
+#pragma unroll
+        for (int i = 0; i < 4; i++) st[8 + i] = st[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) out[i] = gl::canon(st[i]);
+}
+
+__global__ void __launch_bounds__(128) leaves_kernel(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 nrows)
+{
+    const u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    u64 h[4];
+    linear_hash_words(h, input + row * row_ld, row_words);
+    ulonglong2 *o = reinterpret_cast<ulonglong2 *>(leaves + row * 4);
+    o[0] = make_ulonglong2(h[0], h[1]);
+    o[1] = make_ulonglong2(h[2], h[3]);
+}
+
+// merkletree_batch leaves (poseidon_goldilocks.cpp:302-352): linear_hash of every `batch`-column group, then
+// linear_hash over the concatenated 4-word digests.
+__global__ void __launch_bounds__(128) leaves_batch_kernel(u64 *leaves, u64 *digests, const u64 *input, u64 ncols, u64 dim,
+                                                           u64 batch, u64 nbatches, u64 nrows)
+{
+    const u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    u64 *dg = digests + row * nbatches * 4;
+    const u64 *in = input + row * ncols * dim;
+    for (u64 j = 0; j < nbatches; j++)
+    {
+        const u64 nn = (j == nbatches - 1) ? ncols - (nbatches - 1) * batch : batch;
+        u64 h[4];
+        linear_hash_words(h, in + j * batch * dim, nn * dim);
+#pragma unroll
+        for (int i = 0; i < 4; i++) dg[j * 4 + i] = h[i];
+    }
+    u64 h[4];
+    linear_hash_words(h, dg, nbatches * 4);
+#pragma unroll
+    for (int i = 0; i < 4; i++) leaves[row * 4 + i] = h[i];
+}
+
+// one tree level: node i = hash(children 2i, 2i+1 | capacity 0)[0..3]   (poseidon_goldilocks.cpp:283-300)
+__global__ void __launch_bounds__(128) level_kernel(u64 *parents, const u64 *children, u64 nparents)
+{
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nparents) return;
+    u64 st[12];
+    const ulonglong2 *ch = reinterpret_cast<const ulonglong2 *>(children + i * 8);
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+    {
+        ulonglong2 v = ch[k];
+        st[2 * k] = v.x;
+        st[2 * k + 1] = v.y;
+    }
+#pragma unroll
+    for (int k = 8; k < 12; k++) st[k] = 0;
+    poseidon_permute_state(st);
+    ulonglong2 *o = reinterpret_cast<ulonglong2 *>(parents + i * 4);
+    o[0] = make_ulonglong2(gl::canon(st[0]), gl::canon(st[1]));
+    o[1] = make_ulonglong2(gl::canon(st[2]), gl::canon(st[3]));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+static bool g_consts_ready = false;
+int poseidon_init_constants()
+{
+    if (g_consts_ready) return 0;
+    ZK_CUDA(cudaMemcpyToSymbol(c_C, PG_C, sizeof(u64) * 118));
+    ZK_CUDA(cudaMemcpyToSymbol(c_P, PG_P, sizeof(u64) * 144));
+    ZK_CUDA(cudaMemcpyToSymbol(c_S, PG_S, sizeof(u64) * 507));
+    // the kernels hard-code the circulant MDS; check it against the table the reference ships
+    for (int j = 0; j < 12; j++)
+        for (int i = 0; i < 12; i++)
+        {
+            static const u32 row0[12] = {17, 20, 34, 18, 39, 13, 13, 28, 2, 16, 41, 15};
+            u32 e = row0[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
+            if (PG_M[j * 12 + i] != e)
+            {
+                set_error("poseidon: MDS table mismatch at [%d][%d]", j, i);
+                return -1;
+            }
+        }
+    g_consts_ready = true;
+    return 0;
+}
+
+static inline unsigned nblocks(u64 n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+
+int poseidon_permute(u64 *out12, const u64 *in12, u64 n, cudaStream_t st)
+{
+    ZK_TRY(poseidon_init_constants());
+    if (n == 0) return 0;
+    permute_kernel<<<nblocks(n, 128), 128, 0, st>>>(out12, in12, n);
+    ZK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 nrows, cudaStream_t st)
+{
+    ZK_TRY(poseidon_init_constants());
+    if (nrows == 0) return 0;
+    leaves_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, input, row_words, row_ld, nrows);
+    ZK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int merkle_leaves_batch(u64 *leaves, const u64 *input, u64 ncols, u64 dim, u64 batch, u64 nrows, cudaStream_t st)
+{
+    ZK_TRY(poseidon_init_constants());
+    if (nrows == 0) return 0;
+    if (batch == 0)
+    {
+        set_error("merkletree_batch: batch_size 0");
+        return -1;
+    }
+    u64 nbatches = 1;
+    if (ncols > 0) nbatches = (ncols + batch - 1) / batch;
+    u64 *digests = nullptr;
+    ZK_CUDA(cudaMallocAsync(&digests, nrows * nbatches * 4 * sizeof(u64), st));
+    leaves_batch_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, digests, input, ncols, dim, batch, nbatches, nrows);
+    ZK_CUDA(cudaGetLastError());
+    ZK_CUDA(cudaFreeAsync(digests, st));
+    return 0;
+}
+
+int merkle_levels(u64 *tree, u64 nrows, cudaStream_t st)
+{
+    ZK_TRY(poseidon_init_constants());
+    // reference loop (poseidon_goldilocks.cpp:283-300) for a power-of-two number of leaves
+    u64 pending = nrows, next_index = 0;
+    while (pending > 1)
+    {
+        const u64 next_n = pending / 2;
+        level_kernel<<<nblocks(next_n, 128), 128, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
+        ZK_CUDA(cudaGetLastError());
+        next_index += pending * 4;
+        pending /= 2;
+    }
+    return 0;
+}
+
+} // namespace zk
