@@ -37,7 +37,8 @@ def addmod(a, b):
 
 
 def assert_eq(got, want, what=""):
-    assert np.array_equal(np.asarray(got).reshape(-1), np.asarray(want).reshape(-1)), what + " " + first_diff(got, want)
+    if not np.array_equal(np.asarray(got).reshape(-1), np.asarray(want).reshape(-1)):
+        pytest.fail(what + " " + first_diff(got, want), pytrace=False)
 
 
 def gpu_ntt(a, inverse=False, extend=False):

@@ -41,7 +41,7 @@ GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
             "subc.cc.u32 %1, %3, 0;\n\t"
             "subc.u32 m, 0, 0;\n\t"        // m = borrow ? 0xFFFFFFFF : 0
             "sub.cc.u32 %0, %0, m;\n\t"    // t -= eps  (lo + 1, hi - 1 + carry)  when borrow
-            "addc.u32 %1, %1, m;\n\t"
+            "subc.u32 %1, %1, 0;\n\t"
             "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t" // r = t + r2*eps
             "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
             "addc.u32 c, 0, 0;\n\t"        // c = carry out of r
@@ -61,7 +61,7 @@ GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
             "subc.cc.u32 %1, %3, 0;\n\t"
             "subc.u32 m, 0, 0;\n\t"
             "sub.cc.u32 %0, %0, m;\n\t"
-            "addc.u32 %1, %1, m;\n\t"
+            "subc.u32 %1, %1, 0;\n\t"
             "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t"
             "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
             "addc.u32 c, 0, 0;\n\t"
@@ -109,7 +109,7 @@ GL_DEV u64 sub(u64 a, u64 b)
         "subc.cc.u32 %1, %3, %5;\n\t"
         "subc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 %0, %0, m;\n\t"
-        "addc.u32 %1, %1, m;\n\t}"
+        "subc.u32 %1, %1, 0;\n\t}"
         : "=&r"(s0), "=&r"(s1)
         : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
     return pack(s0, s1);
