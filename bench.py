@@ -1,0 +1,366 @@
+#!/usr/bin/env python3
+"""bench.py — the STARK commit hot path on B200: LDE (extendPol) + Poseidon Merkle tree, Mcells/s.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA, libzkgpu.so)
+  python bench.py --impl reference ...                      the reference's own CPU code (oracle/_ref) on host cores
+
+One "step" = one extendAndMerkelize of a synthetic trace (in[i] = splitmix64(seed+i) mod p):
+N=1: 2^23 rows x 665 columns, blowup 2 (BASELINE.json configs[1]); N>1: the same trace column-sharded over N GPUs
+(configs[2]) — total work fixed, so "scaling": "strong".  A cell is one element of the un-extended trace.
+Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for the roofline arithmetic.
+"""
+import argparse
+import ctypes
+import json
+import os
+import pathlib
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = pathlib.Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+SEED = 0x9E3779B97F4A7C15
+METRIC = "lde_merkle_commit_throughput"
+UNIT = "Mcells/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--log-rows", type=int, default=23)
+    ap.add_argument("--cols", type=int, default=665)
+    ap.add_argument("--log-blowup", type=int, default=1)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-log-rows", type=int, default=16, help="rows of the bounded CPU-baseline sample")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "2^%d rows x %d cols, blowup %d, extendPol + Poseidon merkletree" % (a.log_rows, a.cols, 1 << a.log_blowup)
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [l.strip().split(", ") for l in open(self.f.name) if l.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], None, set()
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.strip().lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference leg
+def reference_lib():
+    """oracle/_ref/libzkref.so = the UNMODIFIED reference sources compiled by oracle/Makefile ("kind": "reference");
+    falls back to the plain-C restatement oracle/liboracle.so ("kind": "port")."""
+    p = ROOT / "oracle" / "_ref" / "libzkref.so"
+    if p.exists():
+        return ctypes.CDLL(str(p)), "reference"
+    p = ROOT / "oracle" / "liboracle.so"
+    if not p.exists():
+        subprocess.check_call(["make", "-s", "-f", str(ROOT / "oracle" / "Makefile"), str(p)])
+    return ctypes.CDLL(str(p)), "port"
+
+
+def cpu_commit_once(L, kind, a, out, buf, tree, n, b, c):
+    u64, vp = ctypes.c_uint64, lambda x: x.ctypes.data_as(ctypes.c_void_p)
+    t0 = time.perf_counter()
+    if kind == "reference":
+        L.zkref_extend_pol(vp(out), vp(a), u64(n * b), u64(n), u64(c), vp(buf))
+        t1 = time.perf_counter()
+        L.zkref_merkletree(vp(tree), vp(out), u64(c), u64(n * b), u64(1))
+    else:
+        L.oracle_extend_pol(vp(out), vp(a), u64(n * b), u64(n), u64(c))
+        t1 = time.perf_counter()
+        L.oracle_merkletree(vp(tree), vp(out), u64(c), u64(n * b), u64(1))
+    t2 = time.perf_counter()
+    return t1 - t0, t2 - t1
+
+
+def cpu_sample(args, steps, warmup):
+    """Times the reference CPU path on a bounded sample (same columns / blowup, fewer rows)."""
+    import numpy as np
+    L, kind = reference_lib()
+    cores = os.cpu_count()
+    if kind == "reference":
+        L.zkref_threads.restype = ctypes.c_int
+        cores = L.zkref_threads()
+    n, b, c = 1 << args.cpu_log_rows, 1 << args.log_blowup, args.cols
+    olib = ctypes.CDLL(str(ROOT / "oracle" / "liboracle.so")) if (ROOT / "oracle" / "liboracle.so").exists() else None
+    a = np.empty(n * c, dtype=np.uint64)
+    if olib is not None:
+        olib.oracle_fill(a.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint64(n * c), ctypes.c_uint64(SEED), ctypes.c_uint64(0))
+    else:
+        a[:] = np.arange(n * c, dtype=np.uint64)
+    out = np.zeros(n * b * c, dtype=np.uint64)
+    buf = np.zeros(n * b * c, dtype=np.uint64)
+    tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
+    for _ in range(warmup):
+        cpu_commit_once(L, kind, a, out, buf, tree, n, b, c)
+    lde, mt = [], []
+    for _ in range(steps):
+        t_l, t_m = cpu_commit_once(L, kind, a, out, buf, tree, n, b, c)
+        lde.append(t_l)
+        mt.append(t_m)
+    per = (sum(lde) + sum(mt)) / steps
+    return {"value": n * c / per / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "2^%d rows x %d cols, blowup %d (same columns, fewer rows), %d step(s)" % (args.cpu_log_rows, c, b, steps),
+            "lde_ms": 1e3 * sum(lde) / steps, "merkletree_ms": 1e3 * sum(mt) / steps, "ms_per_step": 1e3 * per}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    t0 = time.time()
+    r = cpu_sample(args, max(1, args.steps), max(0, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "sample": r["sample"]},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "stages_ms": {"STARK_STEP_1_LDE": r["lde_ms"], "STARK_STEP_1_MERKLETREE": r["merkletree_ms"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.time() - t0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import zkevm_prover_b200 as zk
+    from zkevm_prover_b200 import dist_commit as dc
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    zk.init(local)
+    stream = torch.cuda.current_stream()
+    zk.set_stream(stream)
+
+    n, b, c = 1 << args.log_rows, 1 << args.log_blowup, args.cols
+    n_ext = n * b
+    cells = n * c
+    peaks_path = ROOT / "MEASURED_PEAKS.json"
+    if peaks_path.exists():
+        peak_gbs, peak_src = json.loads(peaks_path.read_text())["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak_gbs, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    stage_acc = {}
+    ntt = zk.NTT_Goldilocks(n)
+    if world == 1:
+        d_in = torch.empty(cells, dtype=torch.int64, device="cuda")
+        d_ext = torch.empty(n_ext * c, dtype=torch.int64, device="cuda")
+        d_tree = torch.empty((2 * n_ext - 1) * 4, dtype=torch.int64, device="cuda")
+        zk.fill(d_in, cells, SEED, 0)
+
+        def step(timed):
+            zk.extend_and_merkelize(ntt, d_ext, d_tree, d_in, n_ext, n, c)
+            if timed:
+                for k, v in zk.stage_ms().items():
+                    stage_acc[k] = stage_acc.get(k, 0.0) + v
+    else:
+        ops = dc.GpuOps()
+        cuts = dc.column_cuts(c, world)
+        cg = cuts[rank + 1] - cuts[rank]
+        d_in = torch.empty(max(n * cg, 1), dtype=torch.int64, device="cuda")
+        # rank g holds columns [cuts[g], cuts[g+1]) of the same global trace: element (i, j) = gen(i*C + j)
+        full_row = torch.empty(0)
+        if cg:
+            tmp = torch.empty(min(n, 1 << 16) * c, dtype=torch.int64, device="cuda")
+            rows_per = tmp.numel() // c
+            for r0 in range(0, n, rows_per):
+                zk.fill(tmp, rows_per * c, SEED, r0 * c)
+                zk._check(zk.lib().zkgpu_copy_block(d_in.data_ptr() + 8 * r0 * cg, cg, tmp.data_ptr() + 8 * cuts[rank], c, rows_per, cg))
+            zk.sync()
+            del tmp
+        keep = {}
+
+        def step(timed):
+            ev = []
+
+            def mark(name):
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(stream)
+                ev.append((name, e))
+            rows, tree = dc.commit_sharded(ops, dist, d_in, n, n_ext, c, timers=mark if timed else None)
+            keep["rows"], keep["tree"] = rows, tree
+            if timed:
+                torch.cuda.synchronize()
+                for (_, e0), (name, e1) in zip(ev[:-1], ev[1:]):
+                    stage_acc[name] = stage_acc.get(name, 0.0) + e0.elapsed_time(e1)
+
+    for _ in range(args.warmup):
+        step(False)
+    barrier()
+    launches0 = zk.lib().zkgpu_launch_count()
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step(True)
+    e1.record(stream)
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if sampler else None
+    launches = zk.lib().zkgpu_launch_count() - launches0
+    ms_per_step = ms_total / args.steps
+    value = cells / ms_per_step / 1e3
+    stages = {k: v / args.steps for k, v in stage_acc.items()}
+    root = None
+    if rank == 0:
+        t = d_tree if world == 1 else keep["tree"]
+        root = " ".join("%016x" % (int(x) & (2**64 - 1)) for x in t[-4:].cpu().tolist())
+
+    # ---- end to end through the C ABI with HOST buffers (pinned): H2D of the trace and D2H of the tree every step,
+    # the extended trace stays resident on the device (what getGroupProof / stage 4 read later).
+    e2e = None
+    if not args.no_e2e:
+        if world == 1:
+            h_in = torch.empty(cells, dtype=torch.int64, pin_memory=True)
+            h_in.copy_(d_in)
+            del d_in
+            torch.cuda.empty_cache()
+            h_tree = torch.empty((2 * n_ext - 1) * 4, dtype=torch.int64, pin_memory=True)
+            a_in, a_tree = h_in.data_ptr(), h_tree.data_ptr()
+
+            def e2e_step():
+                zk.extend_and_merkelize(ntt, d_ext, a_tree, a_in, n_ext, n, c)
+            h2d, d2h = cells * 8, h_tree.numel() * 8
+        else:
+            h_in = torch.empty(d_in.numel(), dtype=torch.int64, pin_memory=True)
+            h_in.copy_(d_in)
+            h_tree = torch.empty((2 * n_ext - 1) * 4, dtype=torch.int64, pin_memory=True) if rank == 0 else None
+
+            def e2e_step():
+                d_in.copy_(h_in, non_blocking=True)
+                _, tree = dc.commit_sharded(ops, dist, d_in, n, n_ext, c)
+                if rank == 0:
+                    h_tree.copy_(tree, non_blocking=True)
+                torch.cuda.synchronize()
+            h2d, d2h = cells * 8, ((2 * n_ext - 1) * 4) * 8
+        e2e_step()
+        barrier()
+        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        x0.record(stream)
+        for _ in range(args.e2e_steps):
+            e2e_step()
+        x1.record(stream)
+        barrier()
+        e2e_ms = max_over_ranks(x0.elapsed_time(x1)) / args.e2e_steps
+        e2e = {"value": cells / e2e_ms / 1e3, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
+               "note": "host pinned trace -> device every step, tree -> host every step; extended trace stays device-resident"}
+        if world == 1 and rank == 0:
+            got = " ".join("%016x" % (int(x) & (2**64 - 1)) for x in h_tree[-4:].tolist())
+            assert got == root, "e2e root differs from the device-resident run"
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (leaf hashing: one launch per step on each rank)
+    leaf_ms = stages.get("leaves")
+    leaf_bytes = (8 * c * n_ext + 32 * n_ext) / world  # reads its rows of the extended trace once, writes 4-word digests
+    traffic = None
+    tp = ROOT / "profiles" / "traffic.json"
+    if tp.exists():
+        traffic = json.loads(tp.read_text()).get("leaves_kernel@%dx%d/%d" % (args.log_rows, c, world))
+    achieved = leaf_bytes / (leaf_ms * 1e-3) / 1e9 if leaf_ms else None
+    roofline = {"kernel": "zk::leaves_kernel (Poseidon row sponge)", "bound": "hbm", "achieved": achieved, "peak": peak_gbs,
+                "unit": "GB/s", "frac": achieved / peak_gbs if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": leaf_bytes,
+                "note": "integer-pipe bound kernel (about 1.4e9 Poseidon permutations per step); HBM fraction is low by nature"}
+    lde_ms = stages.get("lde")
+    lde_bytes = 8 * c * (n + n_ext) / world
+    roofline_lde = {"stage": "extendPol (INTT + coset NTTs, all passes)", "bound": "hbm",
+                    "achieved": lde_bytes / (lde_ms * 1e-3) / 1e9 if lde_ms else None, "peak": peak_gbs, "unit": "GB/s",
+                    "frac": lde_bytes / (lde_ms * 1e-3) / 1e9 / peak_gbs if lde_ms else None, "algorithmic_bytes": lde_bytes}
+
+    cpu = None
+    if not args.no_cpu and world == 1:
+        cpu = cpu_sample(args, 1, 1)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample", "lde_ms", "merkletree_ms")}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args), "rows_log2": args.log_rows, "cols": c, "blowup": b,
+                       "parallelism": "1 gpu" if world == 1 else "column-sharded LDE x%d -> NCCL all-to-all -> row-sharded leaf hashing" % world,
+                       "l2": "inputs (%.1f GB) larger than L2, no flush" % (cells * 8 / 1e9)},
+            "stages_ms": {"STARK_STEP_1_LDE": stages.get("lde"), "EXCHANGE": stages.get("exchange"),
+                          "MERKLE_LEAVES": stages.get("leaves"), "MERKLE_NODES": stages.get("nodes"),
+                          "STARK_STEP_1_MERKLETREE": (stages.get("leaves") or 0) + (stages.get("nodes") or 0)},
+            "roofline": roofline, "roofline_lde": roofline_lde, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks, "root": root}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

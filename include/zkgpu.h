@@ -33,6 +33,7 @@ int zkgpu_set_stream(void *cuda_stream); /* cudaStream_t to enqueue on; NULL = t
 int zkgpu_sync(void);                  /* wait for everything enqueued on the library stream */
 const char *zkgpu_last_error(void);
 int zkgpu_device_count(void);
+uint64_t zkgpu_launch_count(void);     /* kernels this library has launched so far in this process */
 int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes);
 /* device-memory helpers so that C/C++ hosts need no CUDA headers */
 int zkgpu_malloc(void **dev_ptr, uint64_t bytes);
@@ -85,8 +86,9 @@ int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t num_c
 
 /* ---- the commit stage as one call: Starks::genProof steps 1-3 (src/starkpil/starks.cpp:51-58, 133-139, 214-220):
  * ntt.extendPol(out_ext, in, NExt, N, ncols) followed by MerkleTreeGL(NExt, ncols, out_ext).merkelize().
- * out_ext: n_extended x ncols, tree: (2*n_extended - 1)*4 words.  With host pointers the trace is streamed
- * through the device in column strips. */
+ * out_ext: n_extended x ncols, tree: (2*n_extended - 1)*4 words.  Here each of the three pointers may independently
+ * be a host or a device pointer (e.g. host trace in, extended trace kept resident on the device for the later
+ * getGroupProof / stage-4 calls, tree back on the host). */
 int zkgpu_extend_and_merkelize(void *ntt, uint64_t *out_ext, uint64_t *tree, const uint64_t *input, uint64_t n_extended,
                                uint64_t n, uint64_t ncols);
 

@@ -10,6 +10,7 @@
 
 namespace zk {
 
+unsigned long long g_launches = 0;
 static thread_local char g_err[512] = "";
 void set_error(const char *fmt, ...)
 {
@@ -121,6 +122,7 @@ int fill_splitmix(u64 *dst, u64 n, u64 seed, u64 offset, cudaStream_t st)
     u64 blocks = (n + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
     fill_kernel<<<(unsigned)blocks, 256, 0, st>>>(dst, n, seed, offset);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -244,6 +246,7 @@ int zkgpu_sync(void)
     return 0;
 }
 const char *zkgpu_last_error(void) { return g_err; }
+uint64_t zkgpu_launch_count(void) { return g_launches; }
 int zkgpu_device_count(void)
 {
     int n = 0;
@@ -352,6 +355,7 @@ int zkgpu_field_op(int op, uint64_t *out, const uint64_t *a, const uint64_t *b, 
     u64 blocks = (n + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
     field_op_kernel<<<(unsigned)blocks, 256, 0, st>>>(op, po, pa, pb, n);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     if (!dev)
     {
@@ -615,6 +619,7 @@ int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64
     u64 blocks = (total + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
     copy_block_kernel<<<(unsigned)blocks, 256, 0, g_ctx.cur>>>(dst, dst_ld, src, src_ld, nrows, ncols);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -629,26 +634,31 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
     NEED_CTX;
     cudaStream_t st = g_ctx.cur;
-    const bool dev = is_device_ptr(tree);
-    if (ncols && (dev != is_device_ptr(input) || dev != is_device_ptr(out_ext)))
-    {
-        set_error("extend_and_merkelize: all pointers must be host or all device");
-        return -1;
-    }
+    // each pointer may independently be host or device: e.g. host trace in, extended trace kept resident on the
+    // device (what getGroupProof / stage 4 need later), tree back on the host.
+    const bool in_dev = ncols == 0 || is_device_ptr(input);
+    const bool out_dev = ncols == 0 || is_device_ptr(out_ext);
+    const bool tree_dev = is_device_ptr(tree);
     const u64 tree_words = (2 * n_ext - 1) * 4;
     Staged din, dout, dtree;
     const u64 *d_in = input;
     u64 *d_out = out_ext, *d_tree = tree;
-    if (!dev)
+    if (!out_dev)
+    {
+        ZK_TRY(dout.alloc(n_ext * ncols));
+        d_out = dout.d;
+    }
+    if (!tree_dev)
+    {
+        ZK_TRY(dtree.alloc(tree_words));
+        d_tree = dtree.d;
+    }
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[4], st));
+    if (!in_dev)
     {
         ZK_TRY(din.alloc(n * ncols));
-        ZK_TRY(dout.alloc(n_ext * ncols));
-        ZK_TRY(dtree.alloc(tree_words));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[4], st));
-        if (ncols) ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
+        ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
         d_in = din.d;
-        d_out = dout.d;
-        d_tree = dtree.d;
     }
     ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
     ZK_TRY(lde_all(d_out, ncols, d_in, ncols, log_n, log_b, ncols, st));
@@ -656,11 +666,11 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     ZK_TRY(merkle_all(d_tree, d_out, ncols, n_ext, st, g_ctx.ev[2]));
     ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
     g_ctx.timed = true;
-    if (!dev)
+    if (!out_dev) ZK_CUDA(cudaMemcpyAsync(out_ext, d_out, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    if (!tree_dev) ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[5], st));
+    if (!in_dev || !out_dev || !tree_dev)
     {
-        if (ncols) ZK_CUDA(cudaMemcpyAsync(out_ext, d_out, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
-        ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[5], st));
         ZK_CUDA(cudaStreamSynchronize(st));
         ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[3], g_ctx.ev[4], g_ctx.ev[0]));
         ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[4], g_ctx.ev[3], g_ctx.ev[5]));

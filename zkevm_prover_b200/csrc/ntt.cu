@@ -303,6 +303,7 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
         ZK_CUDA(cudaMalloc(&d1, (size_t)n1 * sizeof(u64)));
         const u32 n = n1 > 4096 ? n1 : 4096;
         build_pow_tables<<<(n + 255) / 256, 256, 0, st>>>(d0, d1, g, scale, n1);
+        ZK_LAUNCHED();
         ZK_CUDA(cudaGetLastError());
         it = g_tabs.emplace(key, std::make_pair(d0, d1)).first;
     }
@@ -343,6 +344,7 @@ static int launch_pass(const PassParams &P, bool inv, cudaStream_t st)
         ntt_pass_kernel<LR1, LR2, true><<<(unsigned)blocks, Cfg::THREADS, 0, st>>>(P);
     else
         ntt_pass_kernel<LR1, LR2, false><<<(unsigned)blocks, Cfg::THREADS, 0, st>>>(P);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -324,6 +324,7 @@ int poseidon_permute(u64 *out12, const u64 *in12, u64 n, cudaStream_t st)
     ZK_TRY(poseidon_init_constants());
     if (n == 0) return 0;
     permute_kernel<<<nblocks(n, 128), 128, 0, st>>>(out12, in12, n);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -333,6 +334,7 @@ int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 
     ZK_TRY(poseidon_init_constants());
     if (nrows == 0) return 0;
     leaves_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, input, row_words, row_ld, nrows);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -351,6 +353,7 @@ int merkle_leaves_batch(u64 *leaves, const u64 *input, u64 ncols, u64 dim, u64 b
     u64 *digests = nullptr;
     ZK_CUDA(cudaMallocAsync(&digests, nrows * nbatches * 4 * sizeof(u64), st));
     leaves_batch_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, digests, input, ncols, dim, batch, nbatches, nrows);
+    ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     ZK_CUDA(cudaFreeAsync(digests, st));
     return 0;
@@ -365,6 +368,7 @@ int merkle_levels(u64 *tree, u64 nrows, cudaStream_t st)
     {
         const u64 next_n = pending / 2;
         level_kernel<<<nblocks(next_n, 128), 128, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
+        ZK_LAUNCHED();
         ZK_CUDA(cudaGetLastError());
         next_index += pending * 4;
         pending /= 2;

@@ -25,6 +25,10 @@ void set_error(const char *fmt, ...);
         if (r__ < 0) return r__;                                                                   \
     } while (0)
 
+// every kernel launch of the library bumps this (zkgpu_launch_count): evidence for "gpu_launches" in bench.py
+extern unsigned long long g_launches;
+#define ZK_LAUNCHED() (++zk::g_launches)
+
 // ---- NTT (ntt.cu) ----
 enum ScaleMode { SCALE_NONE = 0, SCALE_CONST = 1, SCALE_POWER = 2 };
 
