@@ -20,7 +20,8 @@
 namespace zk {
 
 __constant__ u64 c_C[118];
-__constant__ u64 c_P[144];
+__constant__ u64 c_PT[144]; // transposed: c_PT[i*12 + j] = P[j][i]
+__constant__ u64 c_RC[96]; // constants added after the S-box layer of full round r = 0..7 (row 7 is zero)
 __constant__ u64 c_S[507];
 
 // MDS as the reference applies it: new[i] = sum_j M[j][i] * old[j]  (poseidon_goldilocks.hpp:148-162).
@@ -130,58 +131,58 @@ __device__ __forceinline__ u64 mul_add_nc(u64 a, u64 b, u64 c)
 
 // The reference's hash_full_result on one state (poseidon_goldilocks.cpp:5-37 is the scalar statement).
 // Input words may be any 64-bit value; output words are in [0, 2^64) (callers canonicalise what they store).
+//
+// Code-size matters as much as instruction count here: the SM's L1.5 instruction cache is 32 KB (2048 SASS
+// instructions) and every warp of the SM sits at a different point of the permutation, so a fully unrolled body
+// (7.4k instructions in the first version) spends ~9 cycles per issue waiting for instruction fetch
+// (ncu: stall no_instruction, profiles/r1_*).  All 8 full rounds therefore share ONE loop body
+//     st = pow7(st) + RC[r];  st = MDS * st
+// (RC[7] = 0: the last round adds nothing), with the dense P product and the 22 sparse rounds hanging off
+// iteration r == 3, and the dense P product is a rolled loop over output words.
 __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
 {
 #pragma unroll
     for (int i = 0; i < 12; i++) st[i] = gl::add(st[i], c_C[i]);
 #pragma unroll 1
-    for (int r = 0; r < 3; r++)
+    for (int r = 0; r < 8; r++)
     {
+        const u64 *rc = c_RC + r * 12;
 #pragma unroll
-        for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), c_C[(r + 1) * 12 + i]);
-        mds_small(st);
-    }
-#pragma unroll
-    for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), c_C[48 + i]);
-    {
-        // dense P: new[i] = sum_j P[j][i] * old[j]
+        for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), rc[i]);
+        if (r != 3)
+        {
+            mds_small(st);
+            continue;
+        }
+        // dense P: new[i] = sum_j P[j][i] * old[j]   (c_PT[i][j] = P[j][i])
         u64 nw[12];
-#pragma unroll
+#pragma unroll 1
         for (int i = 0; i < 12; i++)
         {
+            const u64 *pr = c_PT + i * 12;
             Acc160 acc;
             acc.zero();
 #pragma unroll
-            for (int j = 0; j < 12; j++) acc.mac(st[j], c_P[j * 12 + i]);
+            for (int j = 0; j < 12; j++) acc.mac(st[j], pr[j]);
             nw[i] = acc.fold();
         }
 #pragma unroll
         for (int i = 0; i < 12; i++) st[i] = nw[i];
-    }
 #pragma unroll 1
-    for (int r = 0; r < 22; r++)
-    {
-        const u64 *S = c_S + 23 * r;
-        const u64 s0 = gl::add(pow7(st[0]), c_C[60 + r]);
-        Acc160 acc;
-        acc.zero();
-        acc.mac(s0, S[0]);
+        for (int q = 0; q < 22; q++)
+        {
+            const u64 *S = c_S + 23 * q;
+            const u64 s0 = gl::add(pow7(st[0]), c_C[60 + q]);
+            Acc160 acc;
+            acc.zero();
+            acc.mac(s0, S[0]);
 #pragma unroll
-        for (int i = 1; i < 12; i++) acc.mac(st[i], S[i]);
+            for (int i = 1; i < 12; i++) acc.mac(st[i], S[i]);
 #pragma unroll
-        for (int i = 1; i < 12; i++) st[i] = mul_add_nc(s0, S[11 + i], st[i]);
-        st[0] = acc.fold();
+            for (int i = 1; i < 12; i++) st[i] = mul_add_nc(s0, S[11 + i], st[i]);
+            st[0] = acc.fold();
+        }
     }
-#pragma unroll 1
-    for (int r = 0; r < 3; r++)
-    {
-#pragma unroll
-        for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), c_C[82 + r * 12 + i]);
-        mds_small(st);
-    }
-#pragma unroll
-    for (int i = 0; i < 12; i++) st[i] = pow7(st[i]);
-    mds_small(st);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -299,7 +300,20 @@ int poseidon_init_constants()
 {
     if (g_consts_ready) return 0;
     ZK_CUDA(cudaMemcpyToSymbol(c_C, PG_C, sizeof(u64) * 118));
-    ZK_CUDA(cudaMemcpyToSymbol(c_P, PG_P, sizeof(u64) * 144));
+    {
+        u64 pt[144], rc[96];
+        for (int i = 0; i < 12; i++)
+            for (int j = 0; j < 12; j++) pt[i * 12 + j] = PG_P[j * 12 + i];
+        for (int i = 0; i < 12; i++)
+        {
+            for (int r = 0; r < 3; r++) rc[r * 12 + i] = PG_C[(r + 1) * 12 + i];
+            rc[3 * 12 + i] = PG_C[48 + i];
+            for (int r = 0; r < 3; r++) rc[(4 + r) * 12 + i] = PG_C[82 + r * 12 + i];
+            rc[7 * 12 + i] = 0;
+        }
+        ZK_CUDA(cudaMemcpyToSymbol(c_PT, pt, sizeof(pt)));
+        ZK_CUDA(cudaMemcpyToSymbol(c_RC, rc, sizeof(rc)));
+    }
     ZK_CUDA(cudaMemcpyToSymbol(c_S, PG_S, sizeof(u64) * 507));
     // the kernels hard-code the circulant MDS; check it against the table the reference ships
     for (int j = 0; j < 12; j++)
