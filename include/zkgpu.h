@@ -29,7 +29,8 @@ extern "C" {
 
 /* ---- runtime ---- */
 int zkgpu_init(int device);            /* select the device (-1 = keep the current one) and create the context */
-int zkgpu_set_stream(void *cuda_stream); /* cudaStream_t to enqueue on; NULL = the library's own stream */
+int zkgpu_set_stream(void *cuda_stream); /* cudaStream_t to enqueue on (0 = the legacy default stream);
+                                            (void*)-1 = back to the library's own non-blocking stream */
 int zkgpu_sync(void);                  /* wait for everything enqueued on the library stream */
 const char *zkgpu_last_error(void);
 int zkgpu_device_count(void);

@@ -112,7 +112,7 @@ def init(device=-1):
 
 def set_stream(stream=None):
     """Enqueue on `stream` (a torch.cuda.Stream, a raw cudaStream_t integer, or None for the library's own)."""
-    h = None if stream is None else getattr(stream, "cuda_stream", stream)
+    h = ctypes.c_void_p(-1) if stream is None else ctypes.c_void_p(getattr(stream, "cuda_stream", stream))
     _check(lib().zkgpu_set_stream(h))
 
 

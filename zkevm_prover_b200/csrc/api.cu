@@ -235,7 +235,7 @@ int zkgpu_set_stream(void *s)
 {
     LOCK;
     NEED_CTX;
-    g_ctx.cur = s ? (cudaStream_t)s : g_ctx.own;
+    g_ctx.cur = (s == (void *)-1) ? g_ctx.own : (cudaStream_t)s; // 0 is the legacy default stream, a valid choice
     return 0;
 }
 int zkgpu_sync(void)
