@@ -31,6 +31,7 @@
 //   (ntt_goldilocks.cpp:259-277) and keeps every transform at size N.
 #include "gl64.cuh"
 #include "zk_internal.h"
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -85,38 +86,68 @@ __host__ __device__ constexpr int bitrev_c(int x, int bits)
 
 // size-2^LOGE DFT in registers, natural order in and out.  Inputs may be any words in [0, 2^64);
 // outputs are in [0, 2^64) (not canonical).
-template <int LOGE, bool INV>
-__device__ __forceinline__ void dft_regs(u64 (&a)[1 << LOGE])
+// Written with one flat, constant-trip-count loop per stage (template recursion over the stages): with nested
+// variable-bound loops nvcc stopped unrolling at E = 16 and the array went to local memory (LDL/STL in the butterfly
+// loop, ncu source page of the first version).
+template <int LOGE, bool INV, int S>
+struct DftStage
 {
-    constexpr int E = 1 << LOGE;
-#pragma unroll
-    for (int i = 0; i < E; i++)
+    static __device__ __forceinline__ void run(u64 (&a)[1 << LOGE])
     {
-        const int j = bitrev_c(i, LOGE);
-        if (i < j)
+        constexpr int E = 1 << LOGE, m = 1 << S, half = m >> 1;
+#pragma unroll
+        for (int b = 0; b < E / 2; b++)
         {
-            u64 t = a[i];
-            a[i] = a[j];
-            a[j] = t;
+            const int k = (b / half) * m, j = b % half;
+            const int e16 = j * (16 / m);
+            u64 t = (e16 == 0) ? gl::canon(a[k + j + half]) : gl::mul(a[k + j + half], w16_pow<INV>(e16));
+            u64 u = a[k + j];
+            a[k + j] = gl::add(u, t);
+            a[k + j + half] = gl::sub(u, t);
         }
+        DftStage<LOGE, INV, S + 1>::run(a);
     }
-#pragma unroll
-    for (int s = 1; s <= LOGE; s++)
+};
+template <int LOGE, bool INV>
+struct DftStage<LOGE, INV, 5>
+{
+    static __device__ __forceinline__ void run(u64 (&)[1 << LOGE]) {}
+};
+template <int LOGE, bool INV, int S>
+struct DftStageGuard
+{
+    static __device__ __forceinline__ void run(u64 (&a)[1 << LOGE])
     {
-        const int m = 1 << s, half = m >> 1;
-#pragma unroll
-        for (int k = 0; k < E; k += m)
+        if constexpr (S <= LOGE)
         {
+            constexpr int E = 1 << LOGE, m = 1 << S, half = m >> 1;
 #pragma unroll
-            for (int j = 0; j < half; j++)
+            for (int b = 0; b < E / 2; b++)
             {
+                const int k = (b / half) * m, j = b % half;
                 const int e16 = j * (16 / m);
                 u64 t = (e16 == 0) ? gl::canon(a[k + j + half]) : gl::mul(a[k + j + half], w16_pow<INV>(e16));
                 u64 u = a[k + j];
                 a[k + j] = gl::add(u, t);
                 a[k + j + half] = gl::sub(u, t);
             }
+            DftStageGuard<LOGE, INV, S + 1>::run(a);
         }
+    }
+};
+
+template <int LOGE, bool INV>
+__device__ __forceinline__ void dft_regs(u64 (&a)[1 << LOGE])
+{
+    constexpr int E = 1 << LOGE;
+    if constexpr (LOGE > 0)
+    {
+        u64 b[E];
+#pragma unroll
+        for (int i = 0; i < E; i++) b[i] = a[bitrev_c(i, LOGE)];
+#pragma unroll
+        for (int i = 0; i < E; i++) a[i] = b[i];
+        DftStageGuard<LOGE, INV, 1>::run(a);
     }
 }
 
@@ -265,6 +296,10 @@ __global__ void __launch_bounds__(PassCfg<LR1, LR2>::THREADS) ntt_pass_kernel(co
     }
 }
 
+} // namespace zk
+#include "ntt_tile.cuh"
+namespace zk {
+
 // ---------------------------------------------------------------------------------------------------
 // tables
 // ---------------------------------------------------------------------------------------------------
@@ -349,8 +384,58 @@ static int launch_pass(const PassParams &P, bool inv, cudaStream_t st)
     return 0;
 }
 
+static int g_num_sms = 0;
+int g_ntt_force_v1 = 0; // test hook (ZKGPU_NTT_V1=1): always use the simple per-tile kernel
+
+template <int LR1, int LR2>
+static int launch_tile(const PassParams &P, bool inv, cudaStream_t st)
+{
+    using Cfg = TileCfg<LR1, LR2>;
+    static int blocks_per_sm[2] = {0, 0};
+    auto kf = ntt_tile_kernel<LR1, LR2, false>;
+    auto ki = ntt_tile_kernel<LR1, LR2, true>;
+    if (!blocks_per_sm[inv])
+    {
+        if (!g_num_sms)
+        {
+            int dev = 0;
+            ZK_CUDA(cudaGetDevice(&dev));
+            ZK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+        }
+        ZK_CUDA(cudaFuncSetAttribute(inv ? ki : kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        int nb = 0;
+        ZK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, inv ? ki : kf, Cfg::THREADS, Cfg::SMEM));
+        if (nb < 1) nb = 1;
+        blocks_per_sm[inv] = nb;
+    }
+    const u64 ntiles = (P.totalQ + 15) / 16;
+    u64 grid = (u64)g_num_sms * blocks_per_sm[inv];
+    if (grid > ntiles) grid = ntiles;
+    if (grid == 0) return 0;
+    if (inv)
+        ki<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM, st>>>(P, (u32)ntiles);
+    else
+        kf<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM, st>>>(P, (u32)ntiles);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    return 0;
+}
+
 static int dispatch_pass(const PassParams &P, bool inv, cudaStream_t st)
 {
+    static const bool env_v1 = getenv("ZKGPU_NTT_V1") != nullptr;
+    const bool tile_ok = !env_v1 && !g_ntt_force_v1 && P.ncols >= 16 && P.totalQ < 0xFFFFFFF0ull &&
+                         ((u64)P.ncols << P.lgM) < 0xFFFFFFFFull && P.logN <= 30;
+    if (tile_ok)
+    {
+        switch (P.lgNp)
+        {
+        case 5: return launch_tile<3, 2>(P, inv, st);
+        case 6: return launch_tile<3, 3>(P, inv, st);
+        case 7: return launch_tile<4, 3>(P, inv, st);
+        case 8: return launch_tile<4, 4>(P, inv, st);
+        }
+    }
     switch (P.lgNp)
     {
     case 0: return launch_pass<0, 0>(P, inv, st);
