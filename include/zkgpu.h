@@ -72,6 +72,13 @@ int zkgpu_ntt(void *ntt, uint64_t *dst, const uint64_t *src, uint64_t size, uint
 int zkgpu_extend_pol(void *ntt, uint64_t *output, const uint64_t *input, uint64_t n_extended, uint64_t n, uint64_t ncols,
                      uint64_t *buffer);
 
+/* NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305): dst[i*ncols + c] = src[BR(i)*ncols_all + offset_cols + c]
+ * for i < size (BR = bit reversal over log2(size) bits).  When the object was created with extension > 1, rows whose
+ * source offset lies at or beyond (size/extension)*ncols_all are zero-filled (:259-277).  dst == src is allowed only
+ * for extension <= 1 with offset_cols == 0 and ncols == ncols_all (the reference asserts the same, :283, :302). */
+int zkgpu_reverse_permutation(void *ntt, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t offset_cols, uint64_t ncols,
+                              uint64_t ncols_all);
+
 /* ---- PoseidonGoldilocks (src/goldilocks/src/poseidon_goldilocks.hpp:43-81) ---- */
 /* hash_full_result (poseidon_goldilocks.cpp:166-228): n independent 12-word permutations */
 int zkgpu_hash_full_result(uint64_t *out12, const uint64_t *in12, uint64_t n);
@@ -84,6 +91,11 @@ int zkgpu_merkletree(uint64_t *tree, const uint64_t *input, uint64_t num_cols, u
 /* merkletree_batch (poseidon_goldilocks.cpp:302-352) */
 int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size,
                            uint64_t dim);
+
+/* MerkleTreeGL::getGroupProof (src/starkpil/merkleTree/merkleTreeGL.cpp:12-35): proof[0 .. width) = row idx of source,
+ * then for every level below the root the 4-word sibling digest (nodes is the level-major array zkgpu_merkletree
+ * writes).  proof has width + 4*log2(height) words.  source / nodes / proof may each be host or device pointers. */
+int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *nodes, uint64_t width, uint64_t height, uint64_t idx);
 
 /* ---- the commit stage as one call: Starks::genProof steps 1-3 (src/starkpil/starks.cpp:51-58, 133-139, 214-220):
  * ntt.extendPol(out_ext, in, NExt, N, ncols) followed by MerkleTreeGL(NExt, ncols, out_ext).merkelize().

@@ -331,3 +331,48 @@ def test_strip_path_and_properties_large():
     assert_eq(_host(d_out).reshape(n * b, 7), ex[:, 5:12], "column shard")
     # spot-check against the oracle on 3 columns
     assert_eq(ex[:, :3], O.extend_pol(np.ascontiguousarray(x.reshape(n, c)[:, :3]), n * b), "oracle spot check")
+
+
+def test_reverse_permutation_matches_reference_semantics():
+    """NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305): bit-reversed row gather of a column block,
+    zero fill beyond size/extension, and the in-place swap form."""
+    def br(i, bits):
+        return int(format(i, "0%db" % bits)[::-1], 2) if bits else 0
+    size, ncols_all, off, nc = 64, 7, 2, 3
+    src = O.fill(size * ncols_all, SEED, 11).reshape(size, ncols_all)
+    for ext in (1, 4):
+        dst = np.full((size, nc), 123, dtype=np.uint64)
+        zk.NTT_Goldilocks(size, 0, ext).reversePermutation(dst, src, size, off, nc, ncols_all)
+        want = np.zeros_like(dst)
+        for i in range(size):
+            r = br(i, 6)
+            if ext == 1 or r * ncols_all + off < (size // ext) * ncols_all:
+                want[i] = src[r, off:off + nc]
+        assert_eq(dst, want, "reversePermutation ext=%d" % ext)
+    a = src.copy()
+    zk.NTT_Goldilocks(size).reversePermutation(a, a, size, 0, ncols_all, ncols_all)
+    assert_eq(a, src[[br(i, 6) for i in range(size)]], "in place")
+    with pytest.raises(zk.ZkGpuError):
+        zk.NTT_Goldilocks(size, 0, 2).reversePermutation(a, a, size, 0, ncols_all, ncols_all)
+
+
+def test_group_proof_from_device_resident_tree():
+    """the extended trace and the tree stay on the device after the commit; MerkleTreeGL wraps them
+    and serves getRoot / getGroupProof without copying the trace back."""
+    import torch
+    n, c, b = 1 << 10, 21, 2
+    a = O.fill(n * c, SEED, 12).reshape(n, c)
+    d_ext = torch.empty(n * b * c, dtype=torch.int64, device="cuda")
+    d_tree = torch.empty((2 * n * b - 1) * 4, dtype=torch.int64, device="cuda")
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), d_ext, d_tree, a, n * b, n, c)
+    ext = O.extend_pol(a, n * b)
+    tree = O.merkletree(ext, c, n * b)
+    host = zk.MerkleTreeGL(n * b, c, ext.reshape(-1), tree)
+    dev = zk.MerkleTreeGL(n * b, c, d_ext, d_tree)
+    mixed = zk.MerkleTreeGL(n * b, c, d_ext, tree)
+    assert_eq(dev.getRoot(), tree[-4:], "root")
+    for idx in (0, 1, 1000, n * b - 1):
+        want = host.getGroupProof(idx)
+        assert_eq(want[:c], ext[idx], "row")
+        assert_eq(dev.getGroupProof(idx), want, "device proof %d" % idx)
+        assert_eq(mixed.getGroupProof(idx), want, "mixed proof %d" % idx)

@@ -1,0 +1,151 @@
+// int_bench.cu — integer-pipe microbenchmark for the B200 (development aid; results go to profiles/).
+// Measures sustained thread-instructions per clock per SM for the instruction classes the Goldilocks arithmetic
+// is made of, so that the integer "roofline" of the NTT butterflies and of Poseidon can be stated from measurement.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/int_bench tools/int_bench.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../zkevm_prover_b200/csrc/gl64.cuh"
+
+#define ITERS 2048
+
+template <int MODE>
+__global__ void __launch_bounds__(256) k(uint64_t *out, uint32_t seed, long long *cycles)
+{
+    uint32_t a = threadIdx.x * 2654435761u + seed, b = a ^ 0x9e3779b9u;
+    uint64_t x0 = a, x1 = b, x2 = a + 1, x3 = b + 1, x4 = a + 2, x5 = b + 2, x6 = a + 3, x7 = b + 3;
+    uint32_t y0 = a, y1 = b, y2 = a + 5, y3 = b + 5, y4 = a + 6, y5 = b + 6, y6 = a + 7, y7 = b + 7;
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int i = 0; i < ITERS; i++)
+    {
+        if (MODE == 0) // IMAD.WIDE.U32 x8 independent
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                asm volatile("mad.wide.u32 %0, %8, %9, %0;\n\tmad.wide.u32 %1, %8, %9, %1;\n\tmad.wide.u32 %2, %8, %9, %2;\n\t"
+                             "mad.wide.u32 %3, %8, %9, %3;\n\tmad.wide.u32 %4, %8, %9, %4;\n\tmad.wide.u32 %5, %8, %9, %5;\n\t"
+                             "mad.wide.u32 %6, %8, %9, %6;\n\tmad.wide.u32 %7, %8, %9, %7;"
+                             : "+l"(x0), "+l"(x1), "+l"(x2), "+l"(x3), "+l"(x4), "+l"(x5), "+l"(x6), "+l"(x7)
+                             : "r"(a), "r"(b));
+        }
+        else if (MODE == 1) // IMAD (32-bit lo) x8
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                asm volatile("mad.lo.u32 %0, %0, %8, %9;\n\tmad.lo.u32 %1, %1, %8, %9;\n\tmad.lo.u32 %2, %2, %8, %9;\n\t"
+                             "mad.lo.u32 %3, %3, %8, %9;\n\tmad.lo.u32 %4, %4, %8, %9;\n\tmad.lo.u32 %5, %5, %8, %9;\n\t"
+                             "mad.lo.u32 %6, %6, %8, %9;\n\tmad.lo.u32 %7, %7, %8, %9;"
+                             : "+r"(y0), "+r"(y1), "+r"(y2), "+r"(y3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
+                             : "r"(a), "r"(b));
+        }
+        else if (MODE == 2) // IADD3 / LOP3 class: add.u32 with xor to stop folding
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                asm volatile("add.u32 %0, %0, %8;\n\tadd.u32 %1, %1, %9;\n\tadd.u32 %2, %2, %8;\n\tadd.u32 %3, %3, %9;\n\t"
+                             "add.u32 %4, %4, %8;\n\tadd.u32 %5, %5, %9;\n\tadd.u32 %6, %6, %8;\n\tadd.u32 %7, %7, %9;"
+                             : "+r"(y0), "+r"(y1), "+r"(y2), "+r"(y3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
+                             : "r"(a), "r"(b));
+        }
+        else if (MODE == 3) // 1:1 mix IMAD.WIDE + add
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                asm volatile("mad.wide.u32 %0, %8, %9, %0;\n\tadd.u32 %4, %4, %8;\n\tmad.wide.u32 %1, %8, %9, %1;\n\tadd.u32 %5, %5, %9;\n\t"
+                             "mad.wide.u32 %2, %8, %9, %2;\n\tadd.u32 %6, %6, %8;\n\tmad.wide.u32 %3, %8, %9, %3;\n\tadd.u32 %7, %7, %9;"
+                             : "+l"(x0), "+l"(x1), "+l"(x2), "+l"(x3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
+                             : "r"(a), "r"(b));
+        }
+        else if (MODE == 4) // carry chains: add.cc / addc pairs (64-bit adds), 4 pairs
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                asm volatile("add.cc.u32 %0, %0, %8;\n\taddc.u32 %1, %1, %9;\n\tadd.cc.u32 %2, %2, %8;\n\taddc.u32 %3, %3, %9;\n\t"
+                             "add.cc.u32 %4, %4, %8;\n\taddc.u32 %5, %5, %9;\n\tadd.cc.u32 %6, %6, %8;\n\taddc.u32 %7, %7, %9;"
+                             : "+r"(y0), "+r"(y1), "+r"(y2), "+r"(y3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
+                             : "r"(a), "r"(b));
+        }
+        else if (MODE == 5) // mad.lo.cc / madc.hi pairs
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                asm volatile("mad.lo.cc.u32 %0, %8, %9, %0;\n\tmadc.hi.u32 %1, %8, %9, %1;\n\tmad.lo.cc.u32 %2, %8, %9, %2;\n\tmadc.hi.u32 %3, %8, %9, %3;\n\t"
+                             "mad.lo.cc.u32 %4, %8, %9, %4;\n\tmadc.hi.u32 %5, %8, %9, %5;\n\tmad.lo.cc.u32 %6, %8, %9, %6;\n\tmadc.hi.u32 %7, %8, %9, %7;"
+                             : "+r"(y0), "+r"(y1), "+r"(y2), "+r"(y3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
+                             : "r"(a), "r"(b));
+        }
+        else if (MODE == 6) // gl::mul_nc x8 independent chains (32 "instructions" = 32 muls per iteration / 4)
+        {
+            x0 = gl::mul_nc(x0, x1); x1 = gl::mul_nc(x1, x2); x2 = gl::mul_nc(x2, x3); x3 = gl::mul_nc(x3, x4);
+            x4 = gl::mul_nc(x4, x5); x5 = gl::mul_nc(x5, x6); x6 = gl::mul_nc(x6, x7); x7 = gl::mul_nc(x7, x0);
+        }
+        else if (MODE == 7) // gl::mul (canonical)
+        {
+            x0 = gl::mul(x0, x1); x1 = gl::mul(x1, x2); x2 = gl::mul(x2, x3); x3 = gl::mul(x3, x4);
+            x4 = gl::mul(x4, x5); x5 = gl::mul(x5, x6); x6 = gl::mul(x6, x7); x7 = gl::mul(x7, x0);
+        }
+        else if (MODE == 8) // butterfly: t = mul(b, w); a' = a + t; b' = a - t   (4 butterflies)
+        {
+            uint64_t t;
+            t = gl::mul(x1, x4); x1 = gl::sub(x0, t); x0 = gl::add(x0, t);
+            t = gl::mul(x3, x5); x3 = gl::sub(x2, t); x2 = gl::add(x2, t);
+            t = gl::mul(x1, x6); x1 = gl::sub(x2, t); x2 = gl::add(x2, t);
+            t = gl::mul(x3, x7); x3 = gl::sub(x0, t); x0 = gl::add(x0, t);
+        }
+    }
+    long long t1 = clock64();
+    uint64_t s = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7 ^ y0 ^ y1 ^ y2 ^ y3 ^ y4 ^ y5 ^ y6 ^ y7;
+    if (s == 0x1234567) out[0] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) cycles[0] = t1 - t0;
+}
+
+template <int MODE>
+void run(const char *name, double per_iter, uint64_t *out, long long *cyc)
+{
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    for (int warps = 4; warps <= 32; warps *= 2)
+    {
+        // blocks of 256 threads = 8 warps; "warps" resident warps per SM
+        int threads = warps >= 8 ? 256 : warps * 32;
+        int bps = warps >= 8 ? warps / 8 : 1;
+        dim3 grid(sms * bps);
+        k<MODE><<<grid, threads>>>(out, 1, cyc);
+        cudaDeviceSynchronize();
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0);
+        k<MODE><<<grid, threads>>>(out, 2, cyc);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        long long c = 0;
+        cudaMemcpy(&c, cyc, sizeof(c), cudaMemcpyDeviceToHost);
+        double ops = (double)ITERS * per_iter * threads * bps; // per SM
+        printf("%-28s warps/SM=%2d  %.2f ms  cycles=%lld  ops/clk/SM=%.1f  ops/s(total)=%.3e\n", name, warps, ms, c, ops / (double)c,
+               ops * sms / (ms * 1e-3));
+    }
+}
+
+int main()
+{
+    uint64_t *out;
+    long long *cyc;
+    cudaMalloc(&out, 8);
+    cudaMalloc(&cyc, 8);
+    run<0>("IMAD.WIDE.U32", 32, out, cyc);
+    run<1>("IMAD.LO", 32, out, cyc);
+    run<2>("IADD", 32, out, cyc);
+    run<3>("IMAD.WIDE+IADD 1:1", 32, out, cyc);
+    run<4>("add.cc/addc pairs", 32, out, cyc);
+    run<5>("mad.lo.cc/madc.hi pairs", 32, out, cyc);
+    run<6>("gl::mul_nc (muls)", 8, out, cyc);
+    run<7>("gl::mul canonical (muls)", 8, out, cyc);
+    run<8>("butterfly mul+add+sub", 4, out, cyc);
+    cudaError_t e = cudaGetLastError();
+    printf("status: %s\n", cudaGetErrorString(e));
+    return e != cudaSuccess;
+}

@@ -49,6 +49,8 @@ ABI_SYMBOLS = {
     "zkgpu_ntt_destroy": (None, [_vp]),
     "zkgpu_ntt": (_int, [_vp, _vp, _vp, _u64, _u64, _vp, _int, _int]),
     "zkgpu_extend_pol": (_int, [_vp, _vp, _vp, _u64, _u64, _u64, _vp]),
+    "zkgpu_reverse_permutation": (_int, [_vp, _vp, _vp, _u64, _u64, _u64, _u64]),
+    "zkgpu_group_proof": (_int, [_vp, _vp, _vp, _u64, _u64, _u64]),
     "zkgpu_hash_full_result": (_int, [_vp, _vp, _u64]),
     "zkgpu_linear_hash": (_int, [_vp, _vp, _u64]),
     "zkgpu_merkletree": (_int, [_vp, _vp, _u64, _u64, _u64]),
@@ -166,6 +168,9 @@ class NTT_Goldilocks:
     def INTT(self, dst, src, size, ncols=1, buffer=None, nphase=3, nblock=1, extend=False):
         _check(lib().zkgpu_ntt(self._h, _ptr(dst), _ptr(src), size, ncols, _ptr(buffer), 1, int(extend)))
 
+    def reversePermutation(self, dst, src, size, offset_cols, ncols, ncols_all):
+        _check(lib().zkgpu_reverse_permutation(self._h, _ptr(dst), _ptr(src), size, offset_cols, ncols, ncols_all))
+
     def extendPol(self, output, input, N_Extended, N, ncols, buffer=None, nphase=3, nblock=1):
         _check(lib().zkgpu_extend_pol(self._h, _ptr(output), _ptr(input), N_Extended, N, ncols, _ptr(buffer)))
 
@@ -203,10 +208,11 @@ class PoseidonGoldilocks:
 class MerkleTreeGL:
     """Mirror of src/starkpil/merkleTree/merkleTreeGL.hpp:9-79 / .cpp:5-44 for host (numpy) sources."""
 
-    def __init__(self, height, width, source=None):
+    def __init__(self, height, width, source=None, nodes=None):
         self.height, self.width = height, width
         self.source = source if source is not None else np.zeros(height * width, dtype=np.uint64)
-        self.nodes = np.zeros(self.getTreeNumElements(), dtype=np.uint64)
+        # nodes given: wrap caller-owned buffers (e.g. the device-resident tree the commit stage left behind)
+        self.nodes = nodes if nodes is not None else np.zeros(self.getTreeNumElements(), dtype=np.uint64)
 
     def getTreeNumElements(self):
         # MerklehashGoldilocks::getTreeNumElements, merklehash_goldilocks.hpp:15-19
@@ -223,20 +229,16 @@ class MerkleTreeGL:
         PoseidonGoldilocks.merkletree(self.nodes, self.source, self.width, self.height)
 
     def getRoot(self):
-        return self.nodes[self.getTreeNumElements() - 4:].copy()
+        root = np.zeros(4, dtype=np.uint64)
+        _check(lib().zkgpu_memcpy(_ptr(root), _ptr(self.nodes) + 8 * (self.getTreeNumElements() - 4), 32))
+        return root
 
     def getGroupProof(self, idx):
-        """merkleTreeGL.cpp:12-35: the source row followed by the sibling path (4 words per level)."""
-        src = np.asarray(self.source).reshape(self.height, self.width)
-        proof = [src[idx].copy()]
-        offset, n, i = 0, self.height, idx
-        while n > 1:
-            sib = i ^ 1
-            proof.append(self.nodes[offset + sib * 4: offset + sib * 4 + 4].copy())
-            offset += n * 4
-            n >>= 1
-            i >>= 1
-        return np.concatenate(proof)
+        """merkleTreeGL.cpp:12-35: the source row followed by the sibling path (4 words per level); source and nodes may
+        live on the host (numpy) or on the device (torch tensors)."""
+        proof = np.zeros(self.width + 4 * self.MerkleProofSize(), dtype=np.uint64)
+        _check(lib().zkgpu_group_proof(_ptr(proof), _ptr(self.source), _ptr(self.nodes), self.width, self.height, idx))
+        return proof
 
 
 def extend_and_merkelize(ntt, out_ext, tree, inp, N_Extended, N, ncols):

@@ -136,6 +136,53 @@ __global__ void copy_block_kernel(u64 *dst, u64 dst_ld, const u64 *src, u64 src_
     }
 }
 
+// NTT_Goldilocks::reversePermutation: one warp-sized group of threads per destination row
+__global__ void reverse_perm_kernel(u64 *dst, const u64 *src, u64 size, unsigned log_size, u64 offset_cols, u64 ncols, u64 ncols_all,
+                                    u64 ext_limit)
+{
+    const u64 total = size * ncols;
+    for (u64 e = (u64)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (u64)gridDim.x * blockDim.x)
+    {
+        const u64 i = e / ncols, c = e - i * ncols;
+        const u64 r = log_size ? (__brevll(i) >> (64 - log_size)) : 0;
+        const u64 off = r * ncols_all + offset_cols;
+        dst[e] = (off < ext_limit) ? src[off + c] : 0;
+    }
+}
+// in-place variant (dst == src, single block of columns): swap rows i and BR(i) for BR(i) < i
+__global__ void reverse_perm_inplace_kernel(u64 *a, u64 size, unsigned log_size, u64 ncols)
+{
+    const u64 total = size * ncols;
+    for (u64 e = (u64)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (u64)gridDim.x * blockDim.x)
+    {
+        const u64 i = e / ncols, c = e - i * ncols;
+        const u64 r = log_size ? (__brevll(i) >> (64 - log_size)) : 0;
+        if (r < i)
+        {
+            const u64 x = a[i * ncols + c], y = a[r * ncols + c];
+            a[i * ncols + c] = y;
+            a[r * ncols + c] = x;
+        }
+    }
+}
+// MerkleTreeGL::getGroupProof gather: row idx of source, then the sibling digest of every level
+__global__ void group_proof_kernel(u64 *proof, const u64 *row, const u64 *nodes, u64 width, u64 height, u64 idx)
+{
+    for (u64 c = threadIdx.x; c < width; c += blockDim.x) proof[c] = row[c];
+    if (nodes != nullptr && threadIdx.x < 4)
+    {
+        u64 off = 0, n = height, i = idx, lvl = 0;
+        while (n > 1)
+        {
+            proof[width + 4 * lvl + threadIdx.x] = nodes[off + (i ^ 1) * 4 + threadIdx.x];
+            off += n * 4;
+            n >>= 1;
+            i >>= 1;
+            lvl++;
+        }
+    }
+}
+
 __global__ void field_op_kernel(int op, u64 *out, const u64 *a, const u64 *b, u64 n)
 {
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
@@ -437,6 +484,69 @@ int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_
     return 0;
 }
 
+int zkgpu_reverse_permutation(void *h, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t offset_cols, uint64_t ncols,
+                              uint64_t ncols_all)
+{
+    LOCK;
+    if (size == 0 || ncols == 0) return 0;
+    if (!is_pow2(size))
+    {
+        set_error("reversePermutation: size %llu is not a power of two", (unsigned long long)size);
+        return -1;
+    }
+    const int extension = h ? ((NttHandle *)h)->extension : 1;
+    const bool inplace = dst == src || dst == nullptr;
+    if (inplace && (extension > 1 || offset_cols != 0 || ncols != ncols_all))
+    {
+        set_error("reversePermutation: in place needs extension <= 1, offset_cols == 0 and ncols == ncols_all"); // :283, :302
+        return -1;
+    }
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    if (!dst) dst = const_cast<uint64_t *>(src);
+    const unsigned L = ilog2(size);
+    const bool dev = is_device_ptr(src);
+    if (dev != is_device_ptr(dst))
+    {
+        set_error("reversePermutation: dst and src must both be host or both be device pointers");
+        return -1;
+    }
+    // rows of the source the reference may touch: BR(i) < size, i.e. all `size` rows of ncols_all words
+    const u64 src_words = size * ncols_all, dst_words = size * ncols;
+    const u64 ext_limit = extension > 1 ? (size / (u64)extension) * ncols_all : ~(u64)0;
+    Staged ds, dd;
+    const u64 *ps = src;
+    u64 *pd = dst;
+    if (!dev)
+    {
+        const u64 need = extension > 1 ? (ext_limit < src_words ? ext_limit : src_words) : src_words;
+        ZK_TRY(ds.alloc(src_words));
+        ZK_CUDA(cudaMemcpyAsync(ds.d, src, need * sizeof(u64), cudaMemcpyHostToDevice, st));
+        ps = ds.d;
+        if (inplace)
+            pd = ds.d;
+        else
+        {
+            ZK_TRY(dd.alloc(dst_words));
+            pd = dd.d;
+        }
+    }
+    u64 blocks = (dst_words + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    if (inplace)
+        reverse_perm_inplace_kernel<<<(unsigned)blocks, 256, 0, st>>>(pd, size, L, ncols);
+    else
+        reverse_perm_kernel<<<(unsigned)blocks, 256, 0, st>>>(pd, ps, size, L, offset_cols, ncols, ncols_all, ext_limit);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    if (!dev)
+    {
+        ZK_CUDA(cudaMemcpyAsync(dst, pd, dst_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaStreamSynchronize(st));
+    }
+    return 0;
+}
+
 static int check_lde_args(uint64_t n_ext, uint64_t n, unsigned *log_n, unsigned *log_b)
 {
     if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n)
@@ -590,6 +700,61 @@ int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t ncols
 {
     LOCK;
     return merkletree_impl(tree, input, ncols, nrows, batch, dim, true);
+}
+
+int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *nodes, uint64_t width, uint64_t height, uint64_t idx)
+{
+    LOCK;
+    if (height == 0 || idx >= height)
+    {
+        set_error("getGroupProof: idx %llu out of range (height %llu)", (unsigned long long)idx, (unsigned long long)height);
+        return -1;
+    }
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const unsigned levels = ilog2(height);
+    const u64 proof_words = width + 4 * (u64)levels;
+    const bool src_dev = width == 0 || is_device_ptr(source), nodes_dev = levels == 0 || is_device_ptr(nodes), proof_dev = is_device_ptr(proof);
+    if (!src_dev && !nodes_dev && !proof_dev)
+    {
+        // everything on the host: a handful of words, no device work to do (what the reference does, merkleTreeGL.cpp:12-35)
+        for (u64 c = 0; c < width; c++) proof[c] = source[idx * width + c];
+        u64 off = 0, n = height, i = idx;
+        for (unsigned l = 0; l < levels; l++, off += n * 4, n >>= 1, i >>= 1)
+            for (int k = 0; k < 4; k++) proof[width + 4 * l + k] = nodes[off + (i ^ 1) * 4 + k];
+        return 0;
+    }
+    // stage only what the proof needs from host-side buffers
+    Staged drow, dproof;
+    const u64 *d_row = source + idx * width;
+    u64 *d_proof = proof;
+    if (!proof_dev)
+    {
+        ZK_TRY(dproof.alloc(proof_words));
+        d_proof = dproof.d;
+    }
+    if (!src_dev)
+    {
+        ZK_TRY(drow.alloc(width));
+        ZK_CUDA(cudaMemcpyAsync(drow.d, source + idx * width, width * sizeof(u64), cudaMemcpyHostToDevice, st));
+        d_row = drow.d;
+    }
+    if (!nodes_dev)
+    {
+        // host-resident nodes: copy the sibling digests straight into the device proof
+        u64 off = 0, n = height, i = idx;
+        for (unsigned l = 0; l < levels; l++, off += n * 4, n >>= 1, i >>= 1)
+            ZK_CUDA(cudaMemcpyAsync(d_proof + width + 4 * l, nodes + off + (i ^ 1) * 4, 32, cudaMemcpyHostToDevice, st));
+    }
+    group_proof_kernel<<<1, 256, 0, st>>>(d_proof, d_row, nodes_dev ? nodes : nullptr, width, height, idx);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    if (!proof_dev)
+    {
+        ZK_CUDA(cudaMemcpyAsync(proof, d_proof, proof_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaStreamSynchronize(st));
+    }
+    return 0;
 }
 
 int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_words, uint64_t row_ld, uint64_t nrows)
