@@ -44,7 +44,8 @@ int zkgpu_free_host(void *host_ptr);
 int zkgpu_memcpy(void *dst, const void *src, uint64_t bytes); /* any direction, synchronous */
 /* device timings (ms, CUDA events) of the stages of the last commit-type call on this thread's context:
  * [0] LDE (STARK_STEP_k_LDE), [1] Merkle leaves, [2] Merkle node levels (STARK_STEP_k_MERKLETREE = [1]+[2]),
- * [3] host->device staging, [4] device->host staging.  Waits for the stream. */
+ * [3] unused (0), [4] the whole call including host<->device copies when any pointer was a host pointer.  LDE and
+ * leaf absorption run strip by strip, interleaved: [0] and [1] are sums over the strips.  Waits for the stream. */
 int zkgpu_stage_ms(float out[5]);
 
 /* synthetic input generator shared with the CPU oracle: dst[i] = splitmix64(seed + offset + i) mod p */

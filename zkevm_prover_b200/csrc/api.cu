@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 namespace zk {
 
@@ -30,6 +31,15 @@ struct Ctx
     cudaEvent_t ev[8] = {};
     bool timed = false;
     float stage[5] = {0, 0, 0, 0, 0};
+    // strip pipeline (commit_pipeline): copy streams, buffer hand-over events and per-strip timing segments
+    cudaStream_t h2d = nullptr, d2h = nullptr;
+    cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
+    std::vector<cudaEvent_t> pool; // timing events, grown on demand
+    struct Seg
+    {
+        int kind, a, b;
+    };
+    std::vector<Seg> segs; // segments of the last pipelined call: kind 0 = LDE, 1 = leaf absorption
 };
 static Ctx g_ctx;
 static std::recursive_mutex g_mu;
@@ -265,6 +275,156 @@ struct Staged
     }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// The commit stage as a strip pipeline.  Columns are independent in the LDE and the row sponge absorbs columns
+// left to right, so the trace is processed in column strips (multiples of 16 columns):
+//     [host->device copy of strip s+1]  ||  LDE of strip s  ->  leaf absorption of strip s  ||  [device->host of strip s-1]
+// Host-resident input / output strips are double buffered on the device and moved with strided 2-D copies on their
+// own streams; device-resident input / output is used in place.  The running leaf digests live in tree[0 .. 4*NExt).
+// ---------------------------------------------------------------------------------------------------
+static int pipe_event(int *idx, cudaStream_t st)
+{
+    static size_t used = 0;
+    if (idx == nullptr)
+    {
+        used = 0;
+        return 0;
+    }
+    if (used == g_ctx.pool.size())
+    {
+        cudaEvent_t e;
+        ZK_CUDA(cudaEventCreate(&e));
+        g_ctx.pool.push_back(e);
+    }
+    *idx = (int)used++;
+    ZK_CUDA(cudaEventRecord(g_ctx.pool[*idx], st));
+    return 0;
+}
+
+static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *input, bool in_dev, unsigned log_n, unsigned log_b,
+                           u64 ncols, cudaStream_t st)
+{
+    const u64 n = (u64)1 << log_n, n_ext = n << log_b;
+    if (!g_ctx.h2d)
+    {
+        ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.h2d, cudaStreamNonBlocking));
+        ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.d2h, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++)
+        {
+            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_ready[b], cudaEventDisableTiming));
+            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_free[b], cudaEventDisableTiming));
+            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_ready[b], cudaEventDisableTiming));
+            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_free[b], cudaEventDisableTiming));
+        }
+    }
+    // ---- strip width from the memory budget: per column 2n words of LDE scratch, 2n per host-input buffer pair,
+    //      2*NExt per host-output buffer pair
+    size_t free_b = 0, total_b = 0;
+    ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    free_b += g_ctx.scratch_words * sizeof(u64);
+    size_t budget = (size_t)(0.6 * (double)free_b);
+    const size_t cap = (size_t)24 << 30;
+    if (budget > cap) budget = cap;
+    const u64 per_col = 2 * n + (in_dev ? 0 : 2 * n) + (out_dev ? 0 : 2 * n_ext);
+    u64 w = budget / (per_col * sizeof(u64));
+    if (!in_dev || !out_dev)
+    {
+        // enough strips for the copies to overlap the compute
+        u64 target = ((ncols + 5) / 6 + 15) & ~(u64)15;
+        if (target < 16) target = 16;
+        if (w > target) w = target;
+    }
+    if (w >= ncols)
+        w = ncols;
+    else
+    {
+        w &= ~(u64)15;
+        if (w == 0)
+        {
+            set_error("commit: not enough device memory for a 16-column strip of 2^%u rows", log_n);
+            return -4;
+        }
+    }
+    const u64 scratch_words = 2 * n * w, in_words = in_dev ? 0 : n * w, out_words = out_dev ? 0 : n_ext * w;
+    ZK_TRY(ensure_scratch(scratch_words + 2 * in_words + 2 * out_words));
+    u64 *lde_scratch = g_ctx.scratch;
+    u64 *in_buf[2] = {g_ctx.scratch + scratch_words, g_ctx.scratch + scratch_words + in_words};
+    u64 *out_buf[2] = {g_ctx.scratch + scratch_words + 2 * in_words, g_ctx.scratch + scratch_words + 2 * in_words + out_words};
+
+    pipe_event(nullptr, st);
+    g_ctx.segs.clear();
+    const u64 nstrips = (ncols + w - 1) / w;
+    auto strip_cols = [&](u64 s) { return ncols - s * w < w ? ncols - s * w : w; };
+    auto issue_h2d = [&](u64 s) -> int {
+        const int b = (int)(s & 1);
+        const u64 cw = strip_cols(s);
+        if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[b], 0));
+        ZK_CUDA(cudaMemcpy2DAsync(in_buf[b], cw * sizeof(u64), input + s * w, ncols * sizeof(u64), cw * sizeof(u64), n,
+                                  cudaMemcpyHostToDevice, g_ctx.h2d));
+        ZK_CUDA(cudaEventRecord(g_ctx.in_ready[b], g_ctx.h2d));
+        return 0;
+    };
+    if (!in_dev)
+    {
+        // the copy stream must not start before work already queued on the compute stream (e.g. a previous call
+        // still reading the staging buffers) has drained
+        ZK_CUDA(cudaEventRecord(g_ctx.in_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[0], 0));
+        ZK_TRY(issue_h2d(0));
+    }
+    if (!out_dev)
+    {
+        ZK_CUDA(cudaEventRecord(g_ctx.out_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(g_ctx.d2h, g_ctx.out_free[0], 0));
+    }
+    for (u64 s = 0; s < nstrips; s++)
+    {
+        const int b = (int)(s & 1);
+        const u64 c0 = s * w, cw = strip_cols(s);
+        const u64 *src = input + c0;
+        u64 src_ld = ncols;
+        if (!in_dev)
+        {
+            if (s + 1 < nstrips) ZK_TRY(issue_h2d(s + 1));
+            ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.in_ready[b], 0));
+            src = in_buf[b];
+            src_ld = cw;
+        }
+        u64 *dst = out_ext + c0;
+        u64 dst_ld = ncols;
+        if (!out_dev)
+        {
+            if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[b], 0));
+            dst = out_buf[b];
+            dst_ld = cw;
+        }
+        int e0, e1, e2;
+        ZK_TRY(pipe_event(&e0, st));
+        ZK_TRY(lde_strip(dst, dst_ld, src, src_ld, lde_scratch, log_n, log_b, cw, st));
+        ZK_TRY(pipe_event(&e1, st));
+        if (!in_dev) ZK_CUDA(cudaEventRecord(g_ctx.in_free[b], st));
+        ZK_TRY(merkle_absorb(d_tree, dst, cw, dst_ld, n_ext, s == 0, st));
+        ZK_TRY(pipe_event(&e2, st));
+        g_ctx.segs.push_back({0, e0, e1});
+        g_ctx.segs.push_back({1, e1, e2});
+        if (!out_dev)
+        {
+            ZK_CUDA(cudaEventRecord(g_ctx.out_ready[b], st));
+            ZK_CUDA(cudaStreamWaitEvent(g_ctx.d2h, g_ctx.out_ready[b], 0));
+            ZK_CUDA(cudaMemcpy2DAsync(out_ext + c0, ncols * sizeof(u64), out_buf[b], cw * sizeof(u64), cw * sizeof(u64), n_ext,
+                                      cudaMemcpyDeviceToHost, g_ctx.d2h));
+            ZK_CUDA(cudaEventRecord(g_ctx.out_free[b], g_ctx.d2h));
+        }
+    }
+    if (!out_dev)
+    {
+        // the caller-visible completion point is the compute stream: make it wait for the last device->host strips
+        ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[0], 0));
+        ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[1], 0));
+    }
+    return 0;
+}
+
 } // namespace zk
 
 using namespace zk;
@@ -356,6 +516,19 @@ int zkgpu_stage_ms(float out[5])
     LOCK;
     NEED_CTX;
     ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    if (g_ctx.timed && !g_ctx.segs.empty())
+    {
+        g_ctx.stage[0] = g_ctx.stage[1] = 0;
+        for (const auto &sg : g_ctx.segs)
+        {
+            float ms = 0;
+            ZK_CUDA(cudaEventElapsedTime(&ms, g_ctx.pool[sg.a], g_ctx.pool[sg.b]));
+            g_ctx.stage[sg.kind] += ms;
+        }
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[2], g_ctx.ev[2], g_ctx.ev[3]));
+        g_ctx.segs.clear();
+        g_ctx.timed = false;
+    }
     if (g_ctx.timed)
     {
         ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[0], g_ctx.ev[0], g_ctx.ev[1]));
@@ -805,40 +978,55 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     const bool out_dev = ncols == 0 || is_device_ptr(out_ext);
     const bool tree_dev = is_device_ptr(tree);
     const u64 tree_words = (2 * n_ext - 1) * 4;
-    Staged din, dout, dtree;
-    const u64 *d_in = input;
-    u64 *d_out = out_ext, *d_tree = tree;
-    if (!out_dev)
-    {
-        ZK_TRY(dout.alloc(n_ext * ncols));
-        d_out = dout.d;
-    }
+    Staged dtree;
+    u64 *d_tree = tree;
     if (!tree_dev)
     {
         ZK_TRY(dtree.alloc(tree_words));
         d_tree = dtree.d;
     }
     ZK_CUDA(cudaEventRecord(g_ctx.ev[4], st));
-    if (!in_dev)
+    if (ncols <= 4)
     {
-        ZK_TRY(din.alloc(n * ncols));
-        ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
-        d_in = din.d;
+        // rows of <= 4 words are copied, not hashed (poseidon_goldilocks.cpp:234-239): no sponge to pipeline
+        Staged din, dout;
+        const u64 *d_in = input;
+        u64 *d_out = out_ext;
+        if (!in_dev)
+        {
+            ZK_TRY(din.alloc(n * ncols));
+            ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
+            d_in = din.d;
+        }
+        if (!out_dev)
+        {
+            ZK_TRY(dout.alloc(n_ext * ncols));
+            d_out = dout.d;
+        }
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
+        ZK_TRY(lde_all(d_out, ncols, d_in, ncols, log_n, log_b, ncols, st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
+        ZK_TRY(merkle_all(d_tree, d_out, ncols, n_ext, st, g_ctx.ev[2]));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+        g_ctx.segs.clear();
+        if (!out_dev) ZK_CUDA(cudaMemcpyAsync(out_ext, d_out, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        if (!out_dev || !in_dev) ZK_CUDA(cudaStreamSynchronize(st));
     }
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
-    ZK_TRY(lde_all(d_out, ncols, d_in, ncols, log_n, log_b, ncols, st));
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
-    ZK_TRY(merkle_all(d_tree, d_out, ncols, n_ext, st, g_ctx.ev[2]));
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+    else
+    {
+        ZK_TRY(commit_pipeline(out_ext, out_dev, d_tree, input, in_dev, log_n, log_b, ncols, st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+        ZK_TRY(merkle_levels(d_tree, n_ext, st));
+        ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+    }
     g_ctx.timed = true;
-    if (!out_dev) ZK_CUDA(cudaMemcpyAsync(out_ext, d_out, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
     if (!tree_dev) ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
     ZK_CUDA(cudaEventRecord(g_ctx.ev[5], st));
     if (!in_dev || !out_dev || !tree_dev)
     {
         ZK_CUDA(cudaStreamSynchronize(st));
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[3], g_ctx.ev[4], g_ctx.ev[0]));
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[4], g_ctx.ev[3], g_ctx.ev[5]));
+        g_ctx.stage[3] = 0;
+        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[4], g_ctx.ev[4], g_ctx.ev[5])); // whole call on the device clock
     }
     return 0;
 }

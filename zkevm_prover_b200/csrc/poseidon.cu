@@ -26,7 +26,7 @@ __constant__ u64 c_S[507];
 
 // MDS as the reference applies it: new[i] = sum_j M[j][i] * old[j]  (poseidon_goldilocks.hpp:148-162).
 // M is circulant: M[j][i] = circ[(i - j) mod 12] plus 8 on M[0][0].
-__device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
+__host__ __device__ constexpr u32 mds_entry(int j, int i)
 {
     constexpr u32 row0[12] = {17, 20, 34, 18, 39, 13, 13, 28, 2, 16, 41, 15}; // M[0][i] (without the +8 at [0][0])
     return row0[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
@@ -56,7 +56,54 @@ __device__ __forceinline__ u64 fold96(u32 r0, u32 r1, u32 r2)
     return gl::pack(x0, x1);
 }
 
-// st <- M^T-style product of the reference's mvp_ with the small MDS
+// st <- M^T-style product of the reference's mvp_ with the small MDS.
+// Written with explicit mad.wide.u32 (one IMAD.WIDE per 32-bit half and matrix entry, immediates from the template
+// recursion): left to itself nvcc strength-reduces the constant multiplies into shift/LEA/uniform-add sequences that
+// came to 700 SASS instructions per call (profiles/r1_poseidon_notes.md); this form is 288 IMAD.WIDE + 8 per output.
+template <int I, int J>
+struct MdsDot
+{
+    static __device__ __forceinline__ void run(u64 &al, u64 &ah, const u32 (&lo)[12], const u32 (&hi)[12])
+    {
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(al) : "r"(lo[J]), "n"(mds_entry(J, I)));
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(ah) : "r"(hi[J]), "n"(mds_entry(J, I)));
+        MdsDot<I, J + 1>::run(al, ah, lo, hi);
+    }
+};
+template <int I>
+struct MdsDot<I, 12>
+{
+    static __device__ __forceinline__ void run(u64 &, u64 &, const u32 (&)[12], const u32 (&)[12]) {}
+};
+// value = al + ah * 2^32 with al, ah < 2^42  ->  [0, 2^64)
+__device__ __forceinline__ u64 mds_combine(u64 al, u64 ah)
+{
+    u32 r1, r2;
+    asm("add.cc.u32 %0, %2, %3;\n\taddc.u32 %1, %4, 0;" : "=r"(r1), "=r"(r2) : "r"((u32)(al >> 32)), "r"((u32)ah), "r"((u32)(ah >> 32)));
+    return fold96((u32)al, r1, r2);
+}
+template <int I>
+struct MdsRow
+{
+    static __device__ __forceinline__ void run(u64 (&st)[12], const u32 (&lo)[12], const u32 (&hi)[12])
+    {
+        u64 al = 0, ah = 0;
+        MdsDot<I, 0>::run(al, ah, lo, hi);
+        st[I] = mds_combine(al, ah);
+        MdsRow<I + 1>::run(st, lo, hi);
+    }
+};
+template <>
+struct MdsRow<12>
+{
+    static __device__ __forceinline__ void run(u64 (&)[12], const u32 (&)[12], const u32 (&)[12]) {}
+};
+#ifndef ZK_MDS_ASM
+#define ZK_MDS_ASM 1
+#endif
+#ifndef ZK_SBOX_ROLL
+#define ZK_SBOX_ROLL 0
+#endif
 __device__ __forceinline__ void mds_small(u64 (&st)[12])
 {
     u32 lo[12], hi[12];
@@ -66,6 +113,9 @@ __device__ __forceinline__ void mds_small(u64 (&st)[12])
         lo[j] = (u32)st[j];
         hi[j] = (u32)(st[j] >> 32);
     }
+#if ZK_MDS_ASM
+    MdsRow<0>::run(st, lo, hi);
+#else
 #pragma unroll
     for (int i = 0; i < 12; i++)
     {
@@ -76,13 +126,9 @@ __device__ __forceinline__ void mds_small(u64 (&st)[12])
             al += (u64)lo[j] * mds_entry(j, i);
             ah += (u64)hi[j] * mds_entry(j, i);
         }
-        // value = al + ah * 2^32  (al, ah < 2^41)
-        u64 mid = (al >> 32) + (ah & 0xFFFFFFFFull); // < 2^33
-        u32 r0 = (u32)al;
-        u32 r1 = (u32)mid;
-        u32 r2 = (u32)(ah >> 32) + (u32)(mid >> 32);
-        st[i] = fold96(r0, r1, r2);
+        st[i] = mds_combine(al, ah);
     }
+#endif
 }
 
 // 160-bit accumulator for sums of <= 2^32 products of 64-bit words
@@ -147,8 +193,26 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
     for (int r = 0; r < 8; r++)
     {
         const u64 *rc = c_RC + r * 12;
+#if ZK_SBOX_ROLL
+        // S-box layer as 3 iterations over 4 words with a register rotation: a third of the code of the unrolled
+        // layer (the three hot bodies then fit the 32 KB instruction cache together) for 24 moves per iteration
+#pragma unroll 1
+        for (int it = 0; it < 3; it++)
+        {
+#pragma unroll
+            for (int k = 0; k < 4; k++) st[k] = gl::add(pow7(st[k]), rc[4 * it + k]);
+            u64 t0 = st[0], t1 = st[1], t2 = st[2], t3 = st[3];
+#pragma unroll
+            for (int k = 0; k < 8; k++) st[k] = st[k + 4];
+            st[8] = t0;
+            st[9] = t1;
+            st[10] = t2;
+            st[11] = t3;
+        }
+#else
 #pragma unroll
         for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), rc[i]);
+#endif
         if (r != 3)
         {
             mds_small(st);
@@ -200,19 +264,10 @@ __global__ void __launch_bounds__(128) permute_kernel(u64 *out, const u64 *in, u
     for (int i = 0; i < 12; i++) out[t * 12 + i] = gl::canon(st[i]);
 }
 
-// linear_hash of `count` words at p into out[0..3] (canonical).  poseidon_goldilocks.cpp:229-265:
-// count <= 4 is copied (zero padded) and NOT hashed; otherwise sponge with rate 8, capacity = previous out[0..3].
-__device__ __forceinline__ void linear_hash_words(u64 (&out)[4], const u64 *__restrict__ p, u64 count)
+// sponge absorption of `count` (>= 1) words at p, rate 8, starting from capacity st[8..11]; on return st[0..3] is the
+// running digest (un-normalised).  The last chunk is zero padded (poseidon_goldilocks.cpp:244-256).
+__device__ __forceinline__ void sponge_absorb(u64 (&st)[12], const u64 *__restrict__ p, u64 count)
 {
-    if (count <= 4)
-    {
-#pragma unroll
-        for (int i = 0; i < 4; i++) out[i] = (u64)i < count ? gl::canon(p[i]) : 0;
-        return;
-    }
-    u64 st[12];
-#pragma unroll
-    for (int i = 8; i < 12; i++) st[i] = 0;
     u64 done = 0;
     while (done < count)
     {
@@ -232,8 +287,52 @@ __device__ __forceinline__ void linear_hash_words(u64 (&out)[4], const u64 *__re
 #pragma unroll
         for (int i = 0; i < 4; i++) st[8 + i] = st[i];
     }
+}
+
+// linear_hash of `count` words at p into out[0..3] (canonical).  poseidon_goldilocks.cpp:229-265:
+// count <= 4 is copied (zero padded) and NOT hashed; otherwise sponge with rate 8, capacity = previous out[0..3].
+__device__ __forceinline__ void linear_hash_words(u64 (&out)[4], const u64 *__restrict__ p, u64 count)
+{
+    if (count <= 4)
+    {
+#pragma unroll
+        for (int i = 0; i < 4; i++) out[i] = (u64)i < count ? gl::canon(p[i]) : 0;
+        return;
+    }
+    u64 st[12];
+#pragma unroll
+    for (int i = 8; i < 12; i++) st[i] = 0;
+    sponge_absorb(st, p, count);
 #pragma unroll
     for (int i = 0; i < 4; i++) out[i] = gl::canon(st[i]);
+}
+
+// One column strip of the row sponge: row r continues from the digest in leaves[4r..4r+3] (zero for the first strip)
+// and absorbs strip_words words.  Every strip but the last must be a multiple of 8 words wide, so the chunking is the
+// one linear_hash would use on the whole row.  Lets leaf hashing follow the LDE strip by strip (and the host->device
+// copy of the next strip) instead of waiting for the whole extended trace.
+__global__ void __launch_bounds__(128) absorb_kernel(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, int first)
+{
+    const u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    u64 st[12];
+    ulonglong2 *o = reinterpret_cast<ulonglong2 *>(leaves + row * 4);
+    if (first)
+    {
+#pragma unroll
+        for (int i = 8; i < 12; i++) st[i] = 0;
+    }
+    else
+    {
+        const ulonglong2 a = o[0], b = o[1];
+        st[8] = a.x;
+        st[9] = a.y;
+        st[10] = b.x;
+        st[11] = b.y;
+    }
+    sponge_absorb(st, rows + row * row_ld, strip_words);
+    o[0] = make_ulonglong2(gl::canon(st[0]), gl::canon(st[1]));
+    o[1] = make_ulonglong2(gl::canon(st[2]), gl::canon(st[3]));
 }
 
 __global__ void __launch_bounds__(128) leaves_kernel(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 nrows)
@@ -348,6 +447,16 @@ int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 
     ZK_TRY(poseidon_init_constants());
     if (nrows == 0) return 0;
     leaves_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, input, row_words, row_ld, nrows);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st)
+{
+    ZK_TRY(poseidon_init_constants());
+    if (nrows == 0 || strip_words == 0) return 0;
+    absorb_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, rows, strip_words, row_ld, nrows, first ? 1 : 0);
     ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;

@@ -62,6 +62,9 @@ int lde_strip(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, u64 *scratch, unsi
 int poseidon_init_constants();
 // leaves: tree[4*i .. 4*i+3] = linear_hash(input row i), rows of row_words words with stride row_ld
 int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 nrows, cudaStream_t st);
+// one column strip of the row sponge (strip_words a multiple of 8 except for the last strip of a row); the running
+// digest lives in leaves[4*i .. 4*i+3]
+int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st);
 // two-level (batched) leaves: PoseidonGoldilocks::merkletree_batch semantics
 int merkle_leaves_batch(u64 *leaves, const u64 *input, u64 ncols, u64 dim, u64 batch, u64 nrows, cudaStream_t st);
 // all node levels above nrows leaves stored at tree[0 .. 4*nrows): reference level-major layout
