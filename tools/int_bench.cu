@@ -19,25 +19,22 @@ __global__ void __launch_bounds__(256) k(uint64_t *out, uint32_t seed, long long
 #pragma unroll 1
     for (int i = 0; i < ITERS; i++)
     {
-        if (MODE == 0) // IMAD.WIDE.U32 x8 independent
+        if (MODE == 0) // IMAD.WIDE.U32: 8 chains, multiplicand = low word of the neighbouring accumulator (nothing to hoist)
         {
 #pragma unroll
             for (int r = 0; r < 4; r++)
-                asm volatile("mad.wide.u32 %0, %8, %9, %0;\n\tmad.wide.u32 %1, %8, %9, %1;\n\tmad.wide.u32 %2, %8, %9, %2;\n\t"
-                             "mad.wide.u32 %3, %8, %9, %3;\n\tmad.wide.u32 %4, %8, %9, %4;\n\tmad.wide.u32 %5, %8, %9, %5;\n\t"
-                             "mad.wide.u32 %6, %8, %9, %6;\n\tmad.wide.u32 %7, %8, %9, %7;"
-                             : "+l"(x0), "+l"(x1), "+l"(x2), "+l"(x3), "+l"(x4), "+l"(x5), "+l"(x6), "+l"(x7)
-                             : "r"(a), "r"(b));
+            {
+                x0 += (uint64_t)(uint32_t)x1 * b; x1 += (uint64_t)(uint32_t)x2 * b; x2 += (uint64_t)(uint32_t)x3 * b; x3 += (uint64_t)(uint32_t)x4 * b;
+                x4 += (uint64_t)(uint32_t)x5 * b; x5 += (uint64_t)(uint32_t)x6 * b; x6 += (uint64_t)(uint32_t)x7 * b; x7 += (uint64_t)(uint32_t)x0 * b;
+            }
         }
-        else if (MODE == 1) // IMAD (32-bit lo) x8
+        else if (MODE == 1) // IMAD (32-bit): y_i = y_{i+1} * a + y_i
         {
 #pragma unroll
             for (int r = 0; r < 4; r++)
-                asm volatile("mad.lo.u32 %0, %0, %8, %9;\n\tmad.lo.u32 %1, %1, %8, %9;\n\tmad.lo.u32 %2, %2, %8, %9;\n\t"
-                             "mad.lo.u32 %3, %3, %8, %9;\n\tmad.lo.u32 %4, %4, %8, %9;\n\tmad.lo.u32 %5, %5, %8, %9;\n\t"
-                             "mad.lo.u32 %6, %6, %8, %9;\n\tmad.lo.u32 %7, %7, %8, %9;"
-                             : "+r"(y0), "+r"(y1), "+r"(y2), "+r"(y3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
-                             : "r"(a), "r"(b));
+            {
+                y0 += y1 * a; y1 += y2 * a; y2 += y3 * a; y3 += y4 * a; y4 += y5 * a; y5 += y6 * a; y6 += y7 * a; y7 += y0 * a;
+            }
         }
         else if (MODE == 2) // IADD3 / LOP3 class: add.u32 with xor to stop folding
         {
@@ -48,14 +45,14 @@ __global__ void __launch_bounds__(256) k(uint64_t *out, uint32_t seed, long long
                              : "+r"(y0), "+r"(y1), "+r"(y2), "+r"(y3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
                              : "r"(a), "r"(b));
         }
-        else if (MODE == 3) // 1:1 mix IMAD.WIDE + add
+        else if (MODE == 3) // 1:1 mix: IMAD.WIDE chains + 32-bit xor/add chains (ALU)
         {
 #pragma unroll
             for (int r = 0; r < 4; r++)
-                asm volatile("mad.wide.u32 %0, %8, %9, %0;\n\tadd.u32 %4, %4, %8;\n\tmad.wide.u32 %1, %8, %9, %1;\n\tadd.u32 %5, %5, %9;\n\t"
-                             "mad.wide.u32 %2, %8, %9, %2;\n\tadd.u32 %6, %6, %8;\n\tmad.wide.u32 %3, %8, %9, %3;\n\tadd.u32 %7, %7, %9;"
-                             : "+l"(x0), "+l"(x1), "+l"(x2), "+l"(x3), "+r"(y4), "+r"(y5), "+r"(y6), "+r"(y7)
-                             : "r"(a), "r"(b));
+            {
+                x0 += (uint64_t)(uint32_t)x1 * b; y0 = (y0 ^ y1) + a; x1 += (uint64_t)(uint32_t)x2 * b; y1 = (y1 ^ y2) + a;
+                x2 += (uint64_t)(uint32_t)x3 * b; y2 = (y2 ^ y3) + a; x3 += (uint64_t)(uint32_t)x0 * b; y3 = (y3 ^ y0) + a;
+            }
         }
         else if (MODE == 4) // carry chains: add.cc / addc pairs (64-bit adds), 4 pairs
         {
@@ -139,7 +136,7 @@ int main()
     run<0>("IMAD.WIDE.U32", 32, out, cyc);
     run<1>("IMAD.LO", 32, out, cyc);
     run<2>("IADD", 32, out, cyc);
-    run<3>("IMAD.WIDE+IADD 1:1", 32, out, cyc);
+    run<3>("IMAD.WIDE + (LOP3,IADD) 16:32", 48, out, cyc);
     run<4>("add.cc/addc pairs", 32, out, cyc);
     run<5>("mad.lo.cc/madc.hi pairs", 32, out, cyc);
     run<6>("gl::mul_nc (muls)", 8, out, cyc);
