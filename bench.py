@@ -325,18 +325,21 @@ def run_ours(args):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (leaf hashing: one launch per step on each rank)
+    # ---- roofline of the dominant kernel (leaf absorption: one launch per column strip on 1 GPU — the figures below are
+    # per step, i.e. summed over the strips; one launch per step on each rank in the multi-GPU path)
     leaf_ms = stages.get("leaves")
     leaf_bytes = (8 * c * n_ext + 32 * n_ext) / world  # reads its rows of the extended trace once, writes 4-word digests
     traffic = None
     tp = ROOT / "profiles" / "traffic.json"
     if tp.exists():
-        traffic = json.loads(tp.read_text()).get("leaves_kernel@%dx%d/%d" % (args.log_rows, c, world))
+        traffic = json.loads(tp.read_text()).get("absorb_kernel@%dx%d/%d" % (args.log_rows, c, world))
     achieved = leaf_bytes / (leaf_ms * 1e-3) / 1e9 if leaf_ms else None
-    roofline = {"kernel": "zk::leaves_kernel (Poseidon row sponge)", "bound": "hbm", "achieved": achieved, "peak": peak_gbs,
+    roofline = {"kernel": "zk::absorb_kernel (Poseidon row sponge, per step = all strips)" if world == 1 else "zk::leaves_kernel (Poseidon row sponge)", "bound": "hbm", "achieved": achieved, "peak": peak_gbs,
                 "unit": "GB/s", "frac": achieved / peak_gbs if achieved else None, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": leaf_bytes,
-                "note": "integer-pipe bound kernel (about 1.4e9 Poseidon permutations per step); HBM fraction is low by nature"}
+                "permutations_per_s": (n_ext * (-(-c // 8)) / world) / (leaf_ms * 1e-3) if leaf_ms else None,
+                "note": "integer-pipe bound kernel (about 1.4e9 Poseidon permutations per step, 26k SASS instructions each, "
+                        "running at the measured 64-bit modmul chain rate of the SM: profiles/r1_int_bench.txt); HBM fraction is low by nature"}
     lde_ms = stages.get("lde")
     lde_bytes = 8 * c * (n + n_ext) / world
     roofline_lde = {"stage": "extendPol (INTT + coset NTTs, all passes)", "bound": "hbm",

@@ -376,3 +376,57 @@ def test_group_proof_from_device_resident_tree():
         assert_eq(want[:c], ext[idx], "row")
         assert_eq(dev.getGroupProof(idx), want, "device proof %d" % idx)
         assert_eq(mixed.getGroupProof(idx), want, "mixed proof %d" % idx)
+
+
+# ------------------------------------------------------------------------------------------------ large shapes, host pipelines
+def _cpu_commit(a, n_ext, c):
+    """Extended trace and tree from the compiled reference when it travelled to this box, else from the C oracle."""
+    from oracle_lib import Reference
+    R = Reference()
+    X = R if R else O
+    ext = X.extend_pol(a, n_ext)
+    return ext, X.merkletree(ext, c, n_ext)
+
+
+def test_full_width_665_host_pipeline():
+    """SURVEY §8(d) parity case (i): the headline width (665 columns, 83 sponge blocks + 1 ragged word) at 2^16 rows,
+    all three pointers on the HOST: exercises the strip pipeline (6 strips of 112 columns, the last ragged) with
+    host->device and device->host strip copies.  Every word of the extended trace and of the tree is compared."""
+    n, c, b = 1 << 16, 665, 2
+    a = O.fill(n * c, SEED, 21).reshape(n, c)
+    ext = np.zeros((n * b, c), dtype=np.uint64)
+    tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n * b, n, c)
+    want_ext, want_tree = _cpu_commit(a, n * b, c)
+    assert_eq(ext, want_ext, "extended trace")
+    assert_eq(tree, want_tree, "tree")
+    # the same through the two separate reference calls (extendPol, then merkletree) with host pointers
+    ext2 = np.zeros_like(ext)
+    zk.NTT_Goldilocks(n).extendPol(ext2, a, n * b, n, c)
+    assert_eq(ext2, want_ext, "extendPol host strips")
+    assert_eq(gpu_tree(ext2, c, n * b), want_tree, "merkletree host")
+
+
+def test_full_height_2p23_rows():
+    """SURVEY §8(d) parity case (ii): the headline height (2^23 -> 2^24 rows, three 8/8/7-bit NTT passes, 24-level tree)
+    at 24 columns, host trace in (2 strips), extended trace left on the device."""
+    import torch
+    n, c, b = 1 << 23, 24, 2
+    a = O.fill(n * c, SEED, 22).reshape(n, c)
+    d_ext = torch.empty(n * b * c, dtype=torch.int64, device="cuda")
+    tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), d_ext, tree, a, n * b, n, c)
+    want_ext, want_tree = _cpu_commit(a, n * b, c)
+    assert_eq(_host(d_ext), want_ext, "extended trace")
+    assert_eq(tree, want_tree, "tree")
+
+
+def test_merkletree_host_row_chunks():
+    """PoseidonGoldilocks::merkletree with a host source larger than one staging chunk (2^19 x 300 words = 1.26 GB ->
+    two row chunks copied while the previous one is hashed)."""
+    from oracle_lib import Reference
+    rows, c = 1 << 19, 300
+    a = O.fill(rows * c, SEED, 23)
+    R = Reference()
+    want = (R if R else O).merkletree(a, c, rows)
+    assert_eq(gpu_tree(a, c, rows), want, "tree")

@@ -301,22 +301,27 @@ static int pipe_event(int *idx, cudaStream_t st)
     return 0;
 }
 
+static int ensure_pipe_streams()
+{
+    if (g_ctx.h2d) return 0;
+    ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.h2d, cudaStreamNonBlocking));
+    ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.d2h, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++)
+    {
+        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_ready[b], cudaEventDisableTiming));
+        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_free[b], cudaEventDisableTiming));
+        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_ready[b], cudaEventDisableTiming));
+        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_free[b], cudaEventDisableTiming));
+    }
+    return 0;
+}
+
+// d_tree == nullptr: LDE only (extendPol with host pointers)
 static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *input, bool in_dev, unsigned log_n, unsigned log_b,
                            u64 ncols, cudaStream_t st)
 {
     const u64 n = (u64)1 << log_n, n_ext = n << log_b;
-    if (!g_ctx.h2d)
-    {
-        ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.h2d, cudaStreamNonBlocking));
-        ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.d2h, cudaStreamNonBlocking));
-        for (int b = 0; b < 2; b++)
-        {
-            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_ready[b], cudaEventDisableTiming));
-            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_free[b], cudaEventDisableTiming));
-            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_ready[b], cudaEventDisableTiming));
-            ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_free[b], cudaEventDisableTiming));
-        }
-    }
+    ZK_TRY(ensure_pipe_streams());
     // ---- strip width from the memory budget: per column 2n words of LDE scratch, 2n per host-input buffer pair,
     //      2*NExt per host-output buffer pair
     size_t free_b = 0, total_b = 0;
@@ -403,7 +408,7 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
         ZK_TRY(lde_strip(dst, dst_ld, src, src_ld, lde_scratch, log_n, log_b, cw, st));
         ZK_TRY(pipe_event(&e1, st));
         if (!in_dev) ZK_CUDA(cudaEventRecord(g_ctx.in_free[b], st));
-        ZK_TRY(merkle_absorb(d_tree, dst, cw, dst_ld, n_ext, s == 0, st));
+        if (d_tree) ZK_TRY(merkle_absorb(d_tree, dst, cw, dst_ld, n_ext, s == 0, st));
         ZK_TRY(pipe_event(&e2, st));
         g_ctx.segs.push_back({0, e0, e1});
         g_ctx.segs.push_back({1, e1, e2});
@@ -765,6 +770,7 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
     }
     if (dev)
     {
+        g_ctx.segs.clear();
         ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
         ZK_TRY(lde_all(output, ncols, input, ncols, log_n, log_b, ncols, st));
         ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
@@ -773,12 +779,11 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
         g_ctx.timed = true;
         return 0;
     }
-    Staged din, dout;
-    ZK_TRY(din.alloc(n * ncols));
-    ZK_TRY(dout.alloc(n_ext * ncols));
-    ZK_CUDA(cudaMemcpyAsync(din.d, input, n * ncols * sizeof(u64), cudaMemcpyHostToDevice, st));
-    ZK_TRY(lde_all(dout.d, ncols, din.d, ncols, log_n, log_b, ncols, st));
-    ZK_CUDA(cudaMemcpyAsync(output, dout.d, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    // host pointers: column strips, host->device of strip s+1 and device->host of strip s-1 overlap the LDE of strip s
+    ZK_TRY(commit_pipeline(output, false, nullptr, input, false, log_n, log_b, ncols, st));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+    g_ctx.timed = true;
     ZK_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
@@ -828,40 +833,61 @@ static int merkletree_impl(uint64_t *tree, const uint64_t *input, uint64_t ncols
     cudaStream_t st = g_ctx.cur;
     const u64 row_words = ncols * dim;
     const u64 tree_words = (2 * nrows - 1) * 4;
-    const bool dev = is_device_ptr(tree);
-    if (row_words && dev != is_device_ptr(input))
-    {
-        set_error("merkletree: tree and input must both be host or both be device pointers");
-        return -1;
-    }
-    Staged din, dtree;
-    const u64 *d_in = input;
+    const bool tree_dev = is_device_ptr(tree);
+    const bool in_dev = row_words == 0 || is_device_ptr(input);
+    Staged dtree;
     u64 *d_tree = tree;
-    if (!dev)
+    if (!tree_dev)
     {
-        ZK_TRY(din.alloc(nrows * row_words));
         ZK_TRY(dtree.alloc(tree_words));
-        if (row_words) ZK_CUDA(cudaMemcpyAsync(din.d, input, nrows * row_words * sizeof(u64), cudaMemcpyHostToDevice, st));
-        d_in = din.d;
         d_tree = dtree.d;
     }
+    auto leaves_of = [&](u64 *leaves, const u64 *rows, u64 cnt) -> int {
+        if (batched) return merkle_leaves_batch(leaves, rows, ncols, dim, batch, cnt, st);
+        return merkle_leaves(leaves, rows, row_words, row_words, cnt, st);
+    };
     ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
     ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
-    if (batched)
-    {
-        ZK_TRY(merkle_leaves_batch(d_tree, d_in, ncols, dim, batch, nrows, st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
-        ZK_TRY(merkle_levels(d_tree, nrows, st));
-    }
+    g_ctx.segs.clear();
+    if (in_dev)
+        ZK_TRY(leaves_of(d_tree, input, nrows));
     else
-        ZK_TRY(merkle_all(d_tree, d_in, row_words, nrows, st, g_ctx.ev[2]));
+    {
+        // host rows: row chunks (~1 GiB), host->device copy of chunk k+1 overlaps the hashing of chunk k
+        ZK_TRY(ensure_pipe_streams());
+        u64 chunk = ((u64)1 << 27) / row_words;
+        if (chunk == 0) chunk = 1;
+        if (chunk > nrows) chunk = nrows;
+        ZK_TRY(ensure_scratch(2 * chunk * row_words));
+        u64 *buf[2] = {g_ctx.scratch, g_ctx.scratch + chunk * row_words};
+        const u64 nchunks = (nrows + chunk - 1) / chunk;
+        auto issue = [&](u64 k) -> int {
+            const int b = (int)(k & 1);
+            const u64 r0 = k * chunk, cnt = nrows - r0 < chunk ? nrows - r0 : chunk;
+            if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[b], 0));
+            ZK_CUDA(cudaMemcpyAsync(buf[b], input + r0 * row_words, cnt * row_words * sizeof(u64), cudaMemcpyHostToDevice, g_ctx.h2d));
+            ZK_CUDA(cudaEventRecord(g_ctx.in_ready[b], g_ctx.h2d));
+            return 0;
+        };
+        ZK_CUDA(cudaEventRecord(g_ctx.in_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[0], 0));
+        ZK_TRY(issue(0));
+        for (u64 k = 0; k < nchunks; k++)
+        {
+            const int b = (int)(k & 1);
+            const u64 r0 = k * chunk, cnt = nrows - r0 < chunk ? nrows - r0 : chunk;
+            if (k + 1 < nchunks) ZK_TRY(issue(k + 1));
+            ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.in_ready[b], 0));
+            ZK_TRY(leaves_of(d_tree + 4 * r0, buf[b], cnt));
+            ZK_CUDA(cudaEventRecord(g_ctx.in_free[b], st));
+        }
+    }
+    ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+    ZK_TRY(merkle_levels(d_tree, nrows, st));
     ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
     g_ctx.timed = true;
-    if (!dev)
-    {
-        ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
-        ZK_CUDA(cudaStreamSynchronize(st));
-    }
+    if (!tree_dev) ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    if (!tree_dev || !in_dev) ZK_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 int zkgpu_merkletree(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t dim)
