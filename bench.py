@@ -224,22 +224,22 @@ def run_ours(args):
                     stage_acc[k] = stage_acc.get(k, 0.0) + v
     else:
         ops = dc.GpuOps()
-        cuts = dc.column_cuts(c, world)
-        cg = cuts[rank + 1] - cuts[rank]
-        d_in = torch.empty(max(n * cg, 1), dtype=torch.int64, device="cuda")
-        # rank g holds columns [cuts[g], cuts[g+1]) of the same global trace: element (i, j) = gen(i*C + j)
-        full_row = torch.empty(0)
-        if cg:
-            tmp = torch.empty(min(n, 1 << 16) * c, dtype=torch.int64, device="cuda")
-            rows_per = tmp.numel() // c
-            for r0 in range(0, n, rows_per):
-                zk.fill(tmp, rows_per * c, SEED, r0 * c)
-                zk._check(zk.lib().zkgpu_copy_block(d_in.data_ptr() + 8 * r0 * cg, cg, tmp.data_ptr() + 8 * cuts[rank], c, rows_per, cg))
-            zk.sync()
-            del tmp
+        rounds, plan = dc.piece_plan(c, world)
+        # rank g holds, for every round k, columns plan[k][g] of the same global trace: element (i, j) = gen(i*C + j)
+        pieces = [torch.empty(max(n * plan[k][rank][1], 1), dtype=torch.int64, device="cuda") for k in range(rounds)]
+        tmp = torch.empty(min(n, 1 << 16) * c, dtype=torch.int64, device="cuda")
+        rows_per = tmp.numel() // c
+        for r0 in range(0, n, rows_per):
+            zk.fill(tmp, rows_per * c, SEED, r0 * c)
+            for k in range(rounds):
+                c0, w = plan[k][rank]
+                if w:
+                    zk._check(zk.lib().zkgpu_copy_block(pieces[k].data_ptr() + 8 * r0 * w, w, tmp.data_ptr() + 8 * c0, c, rows_per, w))
+        zk.sync()
+        del tmp
         keep = {}
 
-        def step(timed):
+        def step(timed, inputs=None):
             keep.clear()  # the previous step's row shard / tree must be released before the next one allocates
             ev = []
 
@@ -247,7 +247,7 @@ def run_ours(args):
                 e = torch.cuda.Event(enable_timing=True)
                 e.record(stream)
                 ev.append((name, e))
-            rows, tree = dc.commit_sharded(ops, dist, d_in, n, n_ext, c, timers=mark if timed else None)
+            rows, tree = dc.commit_sharded_pipelined(ops, dist, inputs or pieces, n, n_ext, c, rounds, timers=mark if timed else None)
             keep["rows"], keep["tree"] = rows, tree
             if timed:
                 torch.cuda.synchronize()
@@ -292,16 +292,17 @@ def run_ours(args):
                 zk.extend_and_merkelize(ntt, d_ext, a_tree, a_in, n_ext, n, c)
             h2d, d2h = cells * 8, h_tree.numel() * 8
         else:
-            h_in = torch.empty(d_in.numel(), dtype=torch.int64, pin_memory=True)
-            h_in.copy_(d_in)
+            h_pieces = []
+            for k in range(rounds):
+                hp = torch.empty(pieces[k].numel(), dtype=torch.int64, pin_memory=True)
+                hp.copy_(pieces[k])
+                h_pieces.append(hp)
             h_tree = torch.empty((2 * n_ext - 1) * 4, dtype=torch.int64, pin_memory=True) if rank == 0 else None
 
             def e2e_step():
-                keep.clear()
-                d_in.copy_(h_in, non_blocking=True)
-                _, tree = dc.commit_sharded(ops, dist, d_in, n, n_ext, c)
+                step(False, h_pieces)  # pinned host pieces: staged on the copy stream while the previous piece is extended
                 if rank == 0:
-                    h_tree.copy_(tree, non_blocking=True)
+                    h_tree.copy_(keep["tree"], non_blocking=True)
                 torch.cuda.synchronize()
             h2d, d2h = cells * 8, ((2 * n_ext - 1) * 4) * 8
         e2e_step()
@@ -316,7 +317,7 @@ def run_ours(args):
         e2e = {"value": cells / e2e_ms / 1e3, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
                "note": "host pinned trace -> device every step, tree -> host every step; extended trace stays device-resident"}
-        if world == 1 and rank == 0:
+        if rank == 0:
             got = " ".join("%016x" % (int(x) & (2**64 - 1)) for x in h_tree[-4:].tolist())
             assert got == root, "e2e root differs from the device-resident run"
 
@@ -355,9 +356,9 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic",
             "config": {"workload": workload_name(args), "rows_log2": args.log_rows, "cols": c, "blowup": b,
-                       "parallelism": "1 gpu" if world == 1 else "column-sharded LDE x%d -> NCCL all-to-all -> row-sharded leaf hashing" % world,
+                       "parallelism": "1 gpu" if world == 1 else "column pieces (%d rounds) LDE x%d -> NCCL all-to-all per round, overlapped -> row-sharded sponge absorption" % (rounds, world),
                        "l2": "inputs (%.1f GB) larger than L2, no flush" % (cells * 8 / 1e9)},
-            "stages_ms": {"STARK_STEP_1_LDE": stages.get("lde"), "EXCHANGE": stages.get("exchange"),
+            "stages_ms": {"STARK_STEP_1_LDE": stages.get("lde"), "EXCHANGE": stages.get("exchange"),  # N>1: exposed wait only
                           "MERKLE_LEAVES": stages.get("leaves"), "MERKLE_NODES": stages.get("nodes"),
                           "STARK_STEP_1_MERKLETREE": (stages.get("leaves") or 0) + (stages.get("nodes") or 0)},
             "roofline": roofline, "roofline_lde": roofline_lde, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),

@@ -112,6 +112,11 @@ int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64
                       uint64_t ncols);
 /* leaf digests of a row shard (poseidon_goldilocks.cpp:277-281): leaves[4*i..] = linear_hash(row i) */
 int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_words, uint64_t row_ld, uint64_t num_rows);
+/* one column strip of the row sponge (poseidon_goldilocks.cpp:244-256): row i continues from the running digest in
+ * leaves[4*i..] (first != 0: starts from the zero capacity) and absorbs strip_words words found at rows + i*row_ld.
+ * Every strip of a row but the last must be a multiple of 8 words; after the last strip leaves[] holds
+ * linear_hash(row) for rows longer than 4 words. */
+int zkgpu_merkle_absorb(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t num_rows, int first);
 /* node levels above num_rows leaves already stored at tree[0 .. 4*num_rows) (poseidon_goldilocks.cpp:283-300) */
 int zkgpu_merkle_levels(uint64_t *tree, uint64_t num_rows);
 /* gather/scatter between a row-major matrix and a packed block: dst[r*ncols + c] = src[(row0 + r)*src_ld + col0 + c]

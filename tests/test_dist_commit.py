@@ -40,6 +40,23 @@ class OracleOps:
         t = self.O.merkletree(self._np(rows)[:nrows * ncols].copy(), ncols, nrows)
         self._np(tree)[:nrows * 4] = t[:nrows * 4]
 
+    def absorb(self, leaves, block, block_off, width, ld, nrows, first):
+        # running digest after a whole number of 8-word blocks == linear_hash of the row prefix absorbed so far
+        blk = self._np(block)[block_off: block_off + nrows * ld].reshape(nrows, ld)[:, :width]
+        self.prefix = blk.copy() if first else np.concatenate([self.prefix, blk], axis=1)
+        w = self.prefix.shape[1]
+        t = self.O.merkletree(np.ascontiguousarray(self.prefix).reshape(-1), w, nrows)
+        self._np(leaves)[:nrows * 4] = t[:nrows * 4]
+
+    def stage(self, src, slot):
+        return (src, None, slot)
+
+    def staged_wait(self, st):
+        return st[0]
+
+    def staged_release(self, st):
+        pass
+
     def levels(self, tree, nleaves, word_off=0):
         t = self._np(tree)
         lv = dc.subtree_level_offsets(nleaves)
@@ -69,6 +86,58 @@ def _worker(rank, world, port, n, b, c, q):
         q.put((rank, ok_rows, ok_tree))
     finally:
         dist.destroy_process_group()
+
+
+def _worker_pipe(rank, world, port, n, b, c, rounds, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        O = Oracle()
+        full = O.fill(n * c, SEED, 0).reshape(n, c)
+        K, plan = dc.piece_plan(c, world, rounds)
+        pieces = []
+        for k in range(K):
+            c0, w = plan[k][rank]
+            m = np.ascontiguousarray(full[:, c0:c0 + w])
+            pieces.append(torch.from_numpy(m.view(np.int64).reshape(-1).copy()) if w else torch.zeros(1, dtype=torch.int64))
+        rows, tree = dc.commit_sharded_pipelined(OracleOps(), dist, pieces, n, n * b, c, rounds)
+        ext = O.extend_pol(full, n * b)
+        R = n * b // world
+        ok_rows = np.array_equal(rows.numpy().view(np.uint64).reshape(R, c), ext[rank * R:(rank + 1) * R])
+        ok_tree = True
+        if rank == 0:
+            ok_tree = np.array_equal(tree.numpy().view(np.uint64), O.merkletree(ext, c, n * b))
+        q.put((rank, ok_rows, ok_tree))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n,b,c,rounds", [(2, 64, 2, 45, 2), (4, 32, 2, 100, 3), (2, 32, 2, 21, None), (4, 16, 4, 9, None)])
+def test_commit_sharded_pipelined_gloo(world, n, b, c, rounds):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_pipe, args=(r, world, port, n, b, c, rounds, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(60)
+    for rank, ok_rows, ok_tree in res:
+        assert ok_rows, "row shard of rank %d differs" % rank
+        assert ok_tree, "stitched tree differs"
+
+
+def test_piece_plan():
+    K, plan = dc.piece_plan(665, 8)
+    assert K == 3 and plan[0][0] == (0, 32) and plan[2][7] == (648, 17)
+    flat = [p for r in plan for p in r]
+    assert all(a[0] + a[1] == b[0] for a, b in zip(flat[:-1], flat[1:])) and flat[-1][0] + flat[-1][1] == 665
+    assert all(w % 8 == 0 for _, w in flat[:-1])
+    per_rank = [sum(plan[k][g][1] for k in range(K)) for g in range(8)]
+    assert max(per_rank) - min(per_rank) <= 16
+    assert dc.piece_plan(9, 4) == (1, [[(0, 8), (8, 1), (9, 0), (9, 0)]])
 
 
 def _free_port():

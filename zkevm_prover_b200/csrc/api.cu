@@ -962,6 +962,12 @@ int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_wor
     NEED_CTX;
     return merkle_leaves(leaves, rows, row_words, row_ld, nrows, g_ctx.cur);
 }
+int zkgpu_merkle_absorb(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t nrows, int first)
+{
+    LOCK;
+    NEED_CTX;
+    return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, g_ctx.cur);
+}
 int zkgpu_merkle_levels(uint64_t *tree, uint64_t nrows)
 {
     LOCK;

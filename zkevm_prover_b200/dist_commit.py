@@ -59,6 +59,39 @@ class GpuOps:
     def levels(self, tree, nleaves, word_off=0):
         self.zk._check(self.zk.lib().zkgpu_merkle_levels(tree.data_ptr() + 8 * word_off, nleaves))
 
+    def absorb(self, leaves, block, block_off, width, ld, nrows, first):
+        self.zk._check(self.zk.lib().zkgpu_merkle_absorb(leaves.data_ptr(), block.data_ptr() + 8 * block_off, width, ld, nrows, int(first)))
+
+    # ---- host -> device staging of input pieces on a copy stream (two slots), used by commit_sharded_pipelined
+    def stage(self, src, slot):
+        """Start bringing piece `src` (a pinned host tensor, or a device tensor which is used as is) to the device."""
+        if src.is_cuda:
+            return (src, None, slot)
+        torch = self.torch
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream, self._bufs, self._free = torch.cuda.Stream(), [None, None], [None, None]
+        if self._bufs[slot] is None or self._bufs[slot].numel() < src.numel():
+            self._bufs[slot] = torch.empty(src.numel(), dtype=torch.int64, device="cuda")
+        dst = self._bufs[slot][:src.numel()]
+        with torch.cuda.stream(self._copy_stream):
+            if self._free[slot] is not None:
+                self._copy_stream.wait_event(self._free[slot])  # the LDE that last read this slot
+            dst.copy_(src, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        return (dst, ev, slot)
+
+    def staged_wait(self, st):
+        if st[1] is not None:
+            self.torch.cuda.current_stream().wait_event(st[1])
+        return st[0]
+
+    def staged_release(self, st):
+        if st[1] is not None:
+            ev = self.torch.cuda.Event()
+            ev.record(self.torch.cuda.current_stream())
+            self._free[st[2]] = ev
+
 
 def exchange(dist, send, recv, send_splits, recv_splits, group=None):
     """Column shards -> row shards.  NCCL: one all_to_all_single; other backends: pairwise isend/irecv."""
@@ -77,6 +110,133 @@ def exchange(dist, send, recv, send_splits, recv_splits, group=None):
             reqs.append(dist.irecv(recv[ro[h]:ro[h + 1]], h, group=group))
     for r in reqs:
         r.wait()
+
+
+class _Done:
+    def wait(self):
+        return True
+
+
+def exchange_async(dist, send, recv, send_splits, recv_splits, group=None):
+    """exchange() that returns a handle: with NCCL the all-to-all runs on the communicator's stream and handle.wait()
+    makes the current stream wait for it (the host does not block); other backends complete before returning."""
+    if dist.get_backend(group) == "nccl":
+        return dist.all_to_all_single(recv, send, output_split_sizes=recv_splits, input_split_sizes=send_splits, group=group,
+                                      async_op=True)
+    exchange(dist, send, recv, send_splits, recv_splits, group)
+    return _Done()
+
+
+def piece_plan(ncols, world, rounds=None):
+    """Column ownership of the pipelined commit: the row is cut into rounds x world consecutive pieces, piece (k, g)
+    belonging to rank g in round k, every piece a whole number of 8-column sponge blocks (the last one holds the ragged
+    tail).  Returns (rounds, plan) with plan[k][g] = (first column, width).  665 columns on 8 ranks: 3 rounds of
+    pieces 32,32,...,24 columns."""
+    blocks = -(-ncols // 8)
+    if rounds is None:
+        rounds = max(1, min(6, blocks // (3 * world)))
+    pieces = rounds * world
+    base, extra = divmod(blocks, pieces)
+    flat, c0 = [], 0
+    for i in range(pieces):
+        w = min((base + (1 if i < extra else 0)) * 8, ncols - c0)
+        flat.append((c0, w))
+        c0 += w
+    return rounds, [flat[k * world:(k + 1) * world] for k in range(rounds)]
+
+
+def commit_sharded_pipelined(ops, dist, pieces_in, n, n_ext, ncols, rounds=None, group=None, timers=None):
+    """The commit stage over all ranks of `group` as a pipeline over column pieces (piece_plan):
+
+        [host->device of piece k+1]  ||  LDE of piece k  ->  all-to-all of piece k  ||  sponge absorption of round k-1
+
+    Round k's all-to-all hands every rank the columns plan[k][0..G-1] of its rows, which are consecutive in the row, so
+    the row sponge can absorb them as soon as they land while the next round is being extended.
+    pieces_in[k]: this rank's N x width(k, rank) piece of the trace (device tensor, or pinned host tensor which is staged
+    on a copy stream).  Returns (rows, tree) like commit_sharded."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    rounds, plan = piece_plan(ncols, world, rounds)
+    R = n_ext // world
+    assert R * world == n_ext and R >= 1 and (R & (R - 1)) == 0, "NExt must be a power of two >= world size"
+    assert ncols > 4, "rows of <= 4 words are not hashed: use commit_sharded"
+
+    def mark(name):
+        if timers is not None:
+            timers(name)
+
+    mark("start")
+    sub_words = (2 * R - 1) * 4
+    if rank == 0:
+        tree = ops.empty((2 * n_ext - 1) * 4)
+        sub = ops.empty(sub_words)
+    else:
+        tree = sub = ops.empty(sub_words)
+    rows = ops.empty(R * ncols)
+    wmax_mine = max(plan[k][rank][1] for k in range(rounds))
+    wmax_round = max(sum(w for _, w in plan[k]) for k in range(rounds))
+    ext_buf = [ops.empty(max(n_ext * wmax_mine, 1)) for _ in range(min(2, rounds))]
+    recv_buf = [ops.empty(max(R * wmax_round, 1)) for _ in range(min(2, rounds))]
+
+    def finish(k, recv):
+        off = 0
+        for g in range(world):
+            c0, w = plan[k][g]
+            if w:
+                ops.absorb(sub, recv, off, w, w, R, k == 0 and g == 0)
+                ops.copy_block(rows, c0, ncols, recv, off, w, R, w)
+            off += R * w
+        mark("leaves")
+
+    pending = None
+    staged = ops.stage(pieces_in[0], 0)
+    for k in range(rounds):
+        w = plan[k][rank][1]
+        nxt = ops.stage(pieces_in[k + 1], (k + 1) & 1) if k + 1 < rounds else None
+        d_in = ops.staged_wait(staged)
+        mark("h2d_wait")
+        ext, recv = ext_buf[k & 1], recv_buf[k & 1]
+        if w:
+            ops.lde(ext, d_in, n_ext, n, w)
+        ops.staged_release(staged)
+        mark("lde")
+        work = exchange_async(dist, ext[:n_ext * w], recv[:R * sum(x for _, x in plan[k])], [R * w] * world,
+                              [R * x for _, x in plan[k]], group)
+        if pending is not None:
+            pending[0].wait()
+            mark("exchange")
+            finish(pending[1], pending[2])
+        pending = (work, k, recv)
+        staged = nxt
+    pending[0].wait()
+    mark("exchange")
+    finish(pending[1], pending[2])
+    ops.levels(sub, R)
+    tree = _gather_and_stitch(ops, dist, sub, tree, R, n_ext, group)
+    mark("nodes")
+    return rows, tree
+
+
+def _gather_and_stitch(ops, dist, sub, tree, R, n_ext, group=None):
+    """Subtrees -> rank 0, stitched level by level into the reference's level-major array; rank 0 hashes the top."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    sub_words = (2 * R - 1) * 4
+    if world == 1:
+        tree[:sub_words].copy_(sub)
+        return tree
+    if rank == 0:
+        gathered = ops.empty(sub_words * world)
+        parts = [gathered[g * sub_words:(g + 1) * sub_words] for g in range(world)]
+        dist.gather(sub, parts, dst=0, group=group)
+        glob = subtree_level_offsets(n_ext)
+        for lvl, (soff, cnt) in enumerate(subtree_level_offsets(R)):
+            goff = glob[lvl][0]
+            for g in range(world):
+                tree[goff + g * cnt * 4: goff + (g + 1) * cnt * 4].copy_(parts[g][soff: soff + cnt * 4])
+        top_off = glob[len(subtree_level_offsets(R)) - 1][0]
+        ops.levels(tree, world, word_off=top_off)
+    else:
+        dist.gather(sub, None, dst=0, group=group)
+    return tree
 
 
 def commit_sharded(ops, dist, local_in, n, n_ext, ncols, group=None, timers=None):
@@ -121,24 +281,6 @@ def commit_sharded(ops, dist, local_in, n, n_ext, ncols, group=None, timers=None
     ops.leaves(sub, rows, ncols, R)
     mark("leaves")
     ops.levels(sub, R)
-    if world == 1:
-        tree[:sub_words].copy_(sub)
-        mark("nodes")
-        return rows, tree
-    # gather the subtrees on rank 0 and stitch level by level
-    if rank == 0:
-        gathered = ops.empty(sub_words * world)
-        parts = [gathered[g * sub_words:(g + 1) * sub_words] for g in range(world)]
-        dist.gather(sub, parts, dst=0, group=group)
-        glob = subtree_level_offsets(n_ext)
-        for lvl, (soff, cnt) in enumerate(subtree_level_offsets(R)):
-            goff = glob[lvl][0]
-            for g in range(world):
-                tree[goff + g * cnt * 4: goff + (g + 1) * cnt * 4].copy_(parts[g][soff: soff + cnt * 4])
-        # sub-roots now sit contiguously at the level with `world` nodes: finish the top on this GPU
-        top_off = glob[len(subtree_level_offsets(R)) - 1][0]
-        ops.levels(tree, world, word_off=top_off)
-    else:
-        dist.gather(sub, None, dst=0, group=group)
+    tree = _gather_and_stitch(ops, dist, sub, tree, R, n_ext, group)
     mark("nodes")
     return rows, tree
