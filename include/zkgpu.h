@@ -106,6 +106,13 @@ int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *n
 int zkgpu_extend_and_merkelize(void *ntt, uint64_t *out_ext, uint64_t *tree, const uint64_t *input, uint64_t n_extended,
                                uint64_t n, uint64_t ncols);
 
+/* ---- constant-tree builder: the Goldilocks branch of buildConstTree (tools/starkpil/bctree/build_const_tree.cpp:533-596;
+ * interpolate :398-531 is the same LDE as extendPol: 1/N * shift^i pre-scale :361-395, coset shift 7).
+ * image receives the reference's on-disk layout  [nPols, nExt, extended constant polynomials (nExt x nPols, row-major),
+ * tree nodes ((2*nExt-1)*4 words)]  = 2 + nPols*nExt + (2*nExt-1)*4 words, which MerkleTreeGL(Goldilocks::Element *tree)
+ * views directly (merkleTreeGL.hpp:24-32).  const_pols: (1<<n_bits) x n_pols row-major.  Host or device pointers. */
+int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t n_bits, uint64_t n_bits_ext, uint64_t n_pols);
+
 /* ---- multi-GPU building blocks (device pointers only; one process per GPU, the host side does the exchange) ----
  * LDE of a column shard stored with an arbitrary row stride (columns are independent, ntt_goldilocks.cpp:103-110) */
 int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64_t in_ld, uint64_t n_extended, uint64_t n,

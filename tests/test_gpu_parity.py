@@ -430,3 +430,43 @@ def test_merkletree_host_row_chunks():
     R = Reference()
     want = (R if R else O).merkletree(a, c, rows)
     assert_eq(gpu_tree(a, c, rows), want, "tree")
+
+
+def test_build_const_tree_image():
+    """buildConstTree's Goldilocks branch (build_const_tree.cpp:533-596): the file image
+    [nPols, nExt, extended constant pols, nodes] equals header + oracle LDE + oracle tree; MerkleTreeGL views it."""
+    nbits, nbits_ext, npols = 10, 12, 19
+    n, n_ext = 1 << nbits, 1 << nbits_ext
+    a = O.fill(n * npols, SEED, 31).reshape(n, npols)
+    words = 2 + npols * n_ext + (2 * n_ext - 1) * 4
+    img = np.zeros(words, dtype=np.uint64)
+    zk.build_const_tree(img, a, nbits, nbits_ext, npols)
+    ext = O.extend_pol(a, n_ext)
+    assert int(img[0]) == npols and int(img[1]) == n_ext
+    assert_eq(img[2:2 + npols * n_ext], ext, "extended constant pols")
+    assert_eq(img[2 + npols * n_ext:], O.merkletree(ext, npols, n_ext), "tree")
+    import torch
+    d_img = torch.zeros(words, dtype=torch.int64, device="cuda")
+    zk.build_const_tree(d_img, _dev(a), nbits, nbits_ext, npols)
+    zk.sync()
+    assert_eq(_host(d_img), img, "device image")
+
+
+def test_adversarial_value_sets():
+    """all-zero, all p-1, rows of non-canonical words (p, p+1, 2^64-1), single impulse, widths 1..9."""
+    n, b = 1 << 10, 2
+    for c in (1, 2, 3, 4, 5, 7, 8, 9):
+        cases = {
+            "zero": np.zeros((n, c), dtype=np.uint64),
+            "p-1": np.full((n, c), P - 1, dtype=np.uint64),
+            "noncanonical": np.tile(np.array([P, P + 1, 2**64 - 1, 2**64 - 2**32], dtype=np.uint64), n * c // 4 + 1)[:n * c].reshape(n, c),
+            "impulse": np.zeros((n, c), dtype=np.uint64),
+        }
+        cases["impulse"][n // 3, c // 2] = 1
+        for name, a in cases.items():
+            ext = np.zeros((n * b, c), dtype=np.uint64)
+            tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
+            zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n * b, n, c)
+            want = O.extend_pol(a, n * b)
+            assert_eq(ext, want, "%s c=%d ext" % (name, c))
+            assert_eq(tree, O.merkletree(want, c, n * b), "%s c=%d tree" % (name, c))

@@ -18,7 +18,7 @@ import pathlib
 import numpy as np
 
 __all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL",
-           "extend_and_merkelize", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
+           "extend_and_merkelize", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
 
 GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
 _HERE = pathlib.Path(__file__).resolve().parent
@@ -56,6 +56,7 @@ ABI_SYMBOLS = {
     "zkgpu_merkletree": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_merkletree_batch": (_int, [_vp, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_extend_and_merkelize": (_int, [_vp, _vp, _vp, _vp, _u64, _u64, _u64]),
+    "zkgpu_build_const_tree": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_lde_columns": (_int, [_vp, _u64, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_merkle_leaves": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_merkle_absorb": (_int, [_vp, _vp, _u64, _u64, _u64, _int]),
@@ -240,6 +241,12 @@ class MerkleTreeGL:
         proof = np.zeros(self.width + 4 * self.MerkleProofSize(), dtype=np.uint64)
         _check(lib().zkgpu_group_proof(_ptr(proof), _ptr(self.source), _ptr(self.nodes), self.width, self.height, idx))
         return proof
+
+
+def build_const_tree(image, const_pols, nBits, nBitsExt, nPols):
+    """buildConstTree, Goldilocks branch (tools/starkpil/bctree/build_const_tree.cpp:533-596): fills `image` with
+    [nPols, nExt, extended constant polynomials, tree nodes]."""
+    _check(lib().zkgpu_build_const_tree(_ptr(image), _ptr(const_pols), nBits, nBitsExt, nPols))
 
 
 def extend_and_merkelize(ntt, out_ext, tree, inp, N_Extended, N, ncols):

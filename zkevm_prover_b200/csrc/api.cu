@@ -835,6 +835,11 @@ static int merkletree_impl(uint64_t *tree, const uint64_t *input, uint64_t ncols
     const u64 tree_words = (2 * nrows - 1) * 4;
     const bool tree_dev = is_device_ptr(tree);
     const bool in_dev = row_words == 0 || is_device_ptr(input);
+    if (tree_dev && ((uintptr_t)tree & 15))
+    {
+        set_error("merkletree: a device tree pointer must be 16-byte aligned");
+        return -1;
+    }
     Staged dtree;
     u64 *d_tree = tree;
     if (!tree_dev)
@@ -1009,6 +1014,11 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     const bool in_dev = ncols == 0 || is_device_ptr(input);
     const bool out_dev = ncols == 0 || is_device_ptr(out_ext);
     const bool tree_dev = is_device_ptr(tree);
+    if (tree_dev && ((uintptr_t)tree & 15))
+    {
+        set_error("commit: a device tree pointer must be 16-byte aligned");
+        return -1;
+    }
     const u64 tree_words = (2 * n_ext - 1) * 4;
     Staged dtree;
     u64 *d_tree = tree;
@@ -1061,6 +1071,22 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
         ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[4], g_ctx.ev[4], g_ctx.ev[5])); // whole call on the device clock
     }
     return 0;
+}
+
+int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t n_bits, uint64_t n_bits_ext, uint64_t n_pols)
+{
+    LOCK;
+    if (n_bits > 32 || n_bits_ext > 32 || n_bits_ext < n_bits || !image)
+    {
+        set_error("buildConstTree: need nBits <= nBitsExt <= 32 and an image buffer");
+        return -1;
+    }
+    NEED_CTX;
+    const u64 n = (u64)1 << n_bits, n_ext = (u64)1 << n_bits_ext;
+    const u64 header[2] = {n_pols, n_ext}; // constTree[0] = nPols, constTree[1] = nExt (build_const_tree.cpp:576-577)
+    ZK_CUDA(cudaMemcpyAsync(image, header, sizeof(header), cudaMemcpyDefault, g_ctx.cur));
+    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur)); // header[] is a stack buffer
+    return zkgpu_extend_and_merkelize(nullptr, image + 2, image + 2 + n_pols * n_ext, const_pols, n_ext, n, n_pols);
 }
 
 } // extern "C"
