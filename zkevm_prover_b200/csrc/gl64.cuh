@@ -115,6 +115,48 @@ GL_DEV u64 sub(u64 a, u64 b)
     return pack(s0, s1);
 }
 GL_DEV u64 canon(u64 x) { return x >= GL_P ? x - GL_P : x; }
+
+// a * 2^K mod p for 0 < K < 96, canonical result; a may be any 64-bit word.  2 is a 192-th root of unity in this
+// field (2^96 = -1), so the twiddles of every transform of size <= 64 — and in particular w_16 = 2^12, which the
+// in-register radix-16 networks use — are shifts: no multiplier instruction at all.
+// With x = a << (K mod 32) = (x2:x1:x0) the product is  sum x_i * 2^(32 (i + K/32))  and 2^64 = 2^32 - 1, 2^96 = -1,
+// 2^128 = -2^32.
+template <int K>
+GL_DEV u64 mul_pow2(u64 a)
+{
+    static_assert(K > 0 && K < 96, "shift out of range");
+    constexpr int q = K / 32, s = K % 32;
+    const u32 a0 = (u32)a, a1 = (u32)(a >> 32);
+    u32 x0, x1, x2;
+    if (s == 0)
+    {
+        x0 = a0;
+        x1 = a1;
+        x2 = 0;
+    }
+    else
+    {
+        x0 = a0 << s;
+        x1 = __funnelshift_l(a0, a1, s);
+        x2 = a1 >> (32 - s);
+    }
+    if (q == 0) return reduce128<true>(x0, x1, x2, 0u);      // (x1:x0) + x2 * eps
+    if (q == 1) return reduce128<true>(0u, x0, x1, x2);      // x0 * 2^32 + x1 * eps - x2
+    // q == 2:  x0 * eps - x1 - x2 * 2^32  =  (x0:0) - ((x2:x1) + x0);  the minuend is <= p - 1 and the subtrahend < 2^53,
+    // so one conditional "+ p" (= - eps after the 2^64 wrap) gives the canonical value
+    u32 r0, r1;
+    asm("{\n\t.reg .u32 d0, d1, m;\n\t"
+        "add.cc.u32 d0, %3, %2;\n\t"   // d = (x2:x1) + x0
+        "addc.u32 d1, %4, 0;\n\t"
+        "sub.cc.u32 %0, 0, d0;\n\t"    // (x0:0) - d
+        "subc.cc.u32 %1, %2, d1;\n\t"
+        "subc.u32 m, 0, 0;\n\t"        // borrow ? 0xFFFFFFFF : 0
+        "sub.cc.u32 %0, %0, m;\n\t"    // - eps when it wrapped
+        "subc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x0), "r"(x1), "r"(x2));
+    return pack(r0, r1);
+}
 // -x for canonical x
 GL_DEV u64 neg(u64 x) { return x ? GL_P - x : 0; }
 

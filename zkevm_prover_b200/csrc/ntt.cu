@@ -84,6 +84,50 @@ __host__ __device__ constexpr int bitrev_c(int x, int bits)
     return r;
 }
 
+// t = hi * w_16^(+-e) with w_16 = 2^12 as a shift (gl::mul_pow2); the inverse root is -w_16^(8-e), i.e. the same shifts
+// with the two outputs of the butterfly exchanged.
+template <int E16, bool INV>
+__device__ __forceinline__ void butterfly16(u64 &lo, u64 &hi)
+{
+    const u64 u = lo;
+    if constexpr (E16 == 0)
+    {
+        const u64 t = gl::canon(hi);
+        lo = gl::add(u, t);
+        hi = gl::sub(u, t);
+    }
+    else
+    {
+        const u64 t = gl::mul_pow2<12 * (INV ? 8 - E16 : E16)>(hi);
+        if (INV)
+        {
+            lo = gl::sub(u, t);
+            hi = gl::add(u, t);
+        }
+        else
+        {
+            lo = gl::add(u, t);
+            hi = gl::sub(u, t);
+        }
+    }
+}
+// e16 is a compile-time constant after unrolling; dispatch it to the template
+template <bool INV>
+__device__ __forceinline__ void constexpr_butterfly(u64 &lo, u64 &hi, const int e16)
+{
+    switch (e16)
+    {
+    case 0: butterfly16<0, INV>(lo, hi); break;
+    case 1: butterfly16<1, INV>(lo, hi); break;
+    case 2: butterfly16<2, INV>(lo, hi); break;
+    case 3: butterfly16<3, INV>(lo, hi); break;
+    case 4: butterfly16<4, INV>(lo, hi); break;
+    case 5: butterfly16<5, INV>(lo, hi); break;
+    case 6: butterfly16<6, INV>(lo, hi); break;
+    default: butterfly16<7, INV>(lo, hi); break;
+    }
+}
+
 // size-2^LOGE DFT in registers, natural order in and out.  Inputs may be any words in [0, 2^64);
 // outputs are in [0, 2^64) (not canonical).
 // Written with one flat, constant-trip-count loop per stage (template recursion over the stages): with nested
@@ -99,11 +143,7 @@ struct DftStage
         for (int b = 0; b < E / 2; b++)
         {
             const int k = (b / half) * m, j = b % half;
-            const int e16 = j * (16 / m);
-            u64 t = (e16 == 0) ? gl::canon(a[k + j + half]) : gl::mul(a[k + j + half], w16_pow<INV>(e16));
-            u64 u = a[k + j];
-            a[k + j] = gl::add(u, t);
-            a[k + j + half] = gl::sub(u, t);
+            constexpr_butterfly<INV>(a[k + j], a[k + j + half], j * (16 / m));
         }
         DftStage<LOGE, INV, S + 1>::run(a);
     }
@@ -125,11 +165,7 @@ struct DftStageGuard
             for (int b = 0; b < E / 2; b++)
             {
                 const int k = (b / half) * m, j = b % half;
-                const int e16 = j * (16 / m);
-                u64 t = (e16 == 0) ? gl::canon(a[k + j + half]) : gl::mul(a[k + j + half], w16_pow<INV>(e16));
-                u64 u = a[k + j];
-                a[k + j] = gl::add(u, t);
-                a[k + j + half] = gl::sub(u, t);
+                constexpr_butterfly<INV>(a[k + j], a[k + j + half], j * (16 / m));
             }
             DftStageGuard<LOGE, INV, S + 1>::run(a);
         }

@@ -61,25 +61,37 @@ __device__ __noinline__ void tile_step(u64 *buf, int base, int stride, const u64
         for (int j = 0; j < E; j++) a[j] = buf[(base + j * stride) * 16];
     }
     dft_regs<LOGE, INV>(a);
-    if (out.dst == nullptr)
+    const bool scaled = out.dst != nullptr && out.post_mode != SCALE_NONE;
+    if (out.dst == nullptr || scaled)
     {
 #pragma unroll
         for (int k = 0; k < E; k++) buf[(base + k * stride) * 16] = a[k];
+        if (!scaled) return;
+        // Post-scaled output (INTT's 1/N or 7^i/N: zkgpu_ntt only, never the LDE): a rolled loop over the values just
+        // parked in shared memory.  Keeping the three output flavours inside the unrolled store loop tripled the code
+        // of this function and pushed the kernel past the instruction cache (ncu: stall_no_instruction 1.4-1.9).
+        u64 row = out.row0;
+#pragma unroll 1
+        for (int k = 0; k < E; k++)
+        {
+            u64 v = buf[(base + k * stride) * 16];
+            v = out.post_mode == SCALE_CONST ? gl::mul(v, out.post_const) : gl::mul(v, pow2level(out.H0, out.H1, row));
+            out.dst[row * out.dst_ld] = v;
+            row += out.row_step;
+        }
         return;
     }
-    u64 row = out.row0;
-#pragma unroll
-    for (int k = 0; k < E; k++)
+    u64 *d = out.dst + out.row0 * out.dst_ld;
+    const u64 dstep = out.row_step * out.dst_ld;
+    if (out.canon)
     {
-        u64 v = a[k];
-        if (out.post_mode == SCALE_CONST)
-            v = gl::mul(v, out.post_const);
-        else if (out.post_mode == SCALE_POWER)
-            v = gl::mul(v, pow2level(out.H0, out.H1, row));
-        else if (out.canon)
-            v = gl::canon(v);
-        out.dst[row * out.dst_ld] = v;
-        row += out.row_step;
+#pragma unroll
+        for (int k = 0; k < E; k++) d[k * dstep] = gl::canon(a[k]);
+    }
+    else
+    {
+#pragma unroll
+        for (int k = 0; k < E; k++) d[k * dstep] = a[k];
     }
 }
 
