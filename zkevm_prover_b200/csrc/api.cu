@@ -358,13 +358,25 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
 
     pipe_event(nullptr, st);
     g_ctx.segs.clear();
-    const u64 nstrips = (ncols + w - 1) / w;
-    auto strip_cols = [&](u64 s) { return ncols - s * w < w ? ncols - s * w : w; };
+    // strip boundaries: full-width strips of w columns, except that with a host-resident trace the first two strips are
+    // narrow (32, then 64 columns) so that little of the first host->device copy is exposed before compute starts
+    std::vector<u64> start;
+    for (u64 c = 0; c < ncols;)
+    {
+        start.push_back(c);
+        u64 cw = w;
+        if (!in_dev && start.size() == 1 && w > 32) cw = 32;
+        if (!in_dev && start.size() == 2 && w > 64) cw = 64;
+        c += cw;
+    }
+    start.push_back(ncols);
+    const u64 nstrips = start.size() - 1;
+    auto strip_cols = [&](u64 s) { return start[s + 1] - start[s]; };
     auto issue_h2d = [&](u64 s) -> int {
         const int b = (int)(s & 1);
         const u64 cw = strip_cols(s);
         if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[b], 0));
-        ZK_CUDA(cudaMemcpy2DAsync(in_buf[b], cw * sizeof(u64), input + s * w, ncols * sizeof(u64), cw * sizeof(u64), n,
+        ZK_CUDA(cudaMemcpy2DAsync(in_buf[b], cw * sizeof(u64), input + start[s], ncols * sizeof(u64), cw * sizeof(u64), n,
                                   cudaMemcpyHostToDevice, g_ctx.h2d));
         ZK_CUDA(cudaEventRecord(g_ctx.in_ready[b], g_ctx.h2d));
         return 0;
@@ -385,7 +397,7 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
     for (u64 s = 0; s < nstrips; s++)
     {
         const int b = (int)(s & 1);
-        const u64 c0 = s * w, cw = strip_cols(s);
+        const u64 c0 = start[s], cw = strip_cols(s);
         const u64 *src = input + c0;
         u64 src_ld = ncols;
         if (!in_dev)

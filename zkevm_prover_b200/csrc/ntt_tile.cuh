@@ -161,12 +161,16 @@ __global__ void __launch_bounds__(TileCfg<LR1, LR2>::THREADS, 768 / TileCfg<LR1,
         if (L.active)
         {
             const u64 row0 = (L.o << (P.lgNp + P.lgM)) + L.rp;
-            const u64 *s = P.src + L.c;
+            // rows of this thread are TG << lgM apart: one 64-bit pointer increment per element
+            const u64 *s = P.src + L.c + (row0 + ((u64)g << P.lgM)) * P.src_ld;
+            const u64 sstep = ((u64)TG << P.lgM) * P.src_ld;
+            u64 *b = buf + g * 16 + lane;
 #pragma unroll 4
             for (int i = 0; i < Cfg::EPT; i++)
             {
-                const int np = g + TG * i;
-                cp_async8(buf + np * 16 + lane, s + (row0 + ((u64)np << P.lgM)) * P.src_ld);
+                cp_async8(b, s);
+                s += sstep;
+                b += TG * 16;
             }
         }
         cp_async_commit();
