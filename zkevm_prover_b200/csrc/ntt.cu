@@ -86,13 +86,13 @@ __host__ __device__ constexpr int bitrev_c(int x, int bits)
 
 // t = hi * w_16^(+-e) with w_16 = 2^12 as a shift (gl::mul_pow2); the inverse root is -w_16^(8-e), i.e. the same shifts
 // with the two outputs of the butterfly exchanged.
-template <int E16, bool INV>
+template <int E16, bool INV, bool HI_CANON>
 __device__ __forceinline__ void butterfly16(u64 &lo, u64 &hi)
 {
     const u64 u = lo;
     if constexpr (E16 == 0)
     {
-        const u64 t = gl::canon(hi);
+        const u64 t = HI_CANON ? hi : gl::canon(hi); // gl::add / gl::sub need a canonical second operand
         lo = gl::add(u, t);
         hi = gl::sub(u, t);
     }
@@ -112,19 +112,19 @@ __device__ __forceinline__ void butterfly16(u64 &lo, u64 &hi)
     }
 }
 // e16 is a compile-time constant after unrolling; dispatch it to the template
-template <bool INV>
+template <bool INV, bool HI_CANON>
 __device__ __forceinline__ void constexpr_butterfly(u64 &lo, u64 &hi, const int e16)
 {
     switch (e16)
     {
-    case 0: butterfly16<0, INV>(lo, hi); break;
-    case 1: butterfly16<1, INV>(lo, hi); break;
-    case 2: butterfly16<2, INV>(lo, hi); break;
-    case 3: butterfly16<3, INV>(lo, hi); break;
-    case 4: butterfly16<4, INV>(lo, hi); break;
-    case 5: butterfly16<5, INV>(lo, hi); break;
-    case 6: butterfly16<6, INV>(lo, hi); break;
-    default: butterfly16<7, INV>(lo, hi); break;
+    case 0: butterfly16<0, INV, HI_CANON>(lo, hi); break;
+    case 1: butterfly16<1, INV, false>(lo, hi); break;
+    case 2: butterfly16<2, INV, false>(lo, hi); break;
+    case 3: butterfly16<3, INV, false>(lo, hi); break;
+    case 4: butterfly16<4, INV, false>(lo, hi); break;
+    case 5: butterfly16<5, INV, false>(lo, hi); break;
+    case 6: butterfly16<6, INV, false>(lo, hi); break;
+    default: butterfly16<7, INV, false>(lo, hi); break;
     }
 }
 
@@ -133,27 +133,7 @@ __device__ __forceinline__ void constexpr_butterfly(u64 &lo, u64 &hi, const int 
 // Written with one flat, constant-trip-count loop per stage (template recursion over the stages): with nested
 // variable-bound loops nvcc stopped unrolling at E = 16 and the array went to local memory (LDL/STL in the butterfly
 // loop, ncu source page of the first version).
-template <int LOGE, bool INV, int S>
-struct DftStage
-{
-    static __device__ __forceinline__ void run(u64 (&a)[1 << LOGE])
-    {
-        constexpr int E = 1 << LOGE, m = 1 << S, half = m >> 1;
-#pragma unroll
-        for (int b = 0; b < E / 2; b++)
-        {
-            const int k = (b / half) * m, j = b % half;
-            constexpr_butterfly<INV>(a[k + j], a[k + j + half], j * (16 / m));
-        }
-        DftStage<LOGE, INV, S + 1>::run(a);
-    }
-};
-template <int LOGE, bool INV>
-struct DftStage<LOGE, INV, 5>
-{
-    static __device__ __forceinline__ void run(u64 (&)[1 << LOGE]) {}
-};
-template <int LOGE, bool INV, int S>
+template <int LOGE, bool INV, int S, bool CANON_IN>
 struct DftStageGuard
 {
     static __device__ __forceinline__ void run(u64 (&a)[1 << LOGE])
@@ -165,14 +145,15 @@ struct DftStageGuard
             for (int b = 0; b < E / 2; b++)
             {
                 const int k = (b / half) * m, j = b % half;
-                constexpr_butterfly<INV>(a[k + j], a[k + j + half], j * (16 / m));
+                // the first stage reads the caller's values: canonical when CANON_IN
+                constexpr_butterfly<INV, (CANON_IN && S == 1)>(a[k + j], a[k + j + half], j * (16 / m));
             }
-            DftStageGuard<LOGE, INV, S + 1>::run(a);
+            DftStageGuard<LOGE, INV, S + 1, CANON_IN>::run(a);
         }
     }
 };
 
-template <int LOGE, bool INV>
+template <int LOGE, bool INV, bool CANON_IN = false>
 __device__ __forceinline__ void dft_regs(u64 (&a)[1 << LOGE])
 {
     constexpr int E = 1 << LOGE;
@@ -183,7 +164,7 @@ __device__ __forceinline__ void dft_regs(u64 (&a)[1 << LOGE])
         for (int i = 0; i < E; i++) b[i] = a[bitrev_c(i, LOGE)];
 #pragma unroll
         for (int i = 0; i < E; i++) a[i] = b[i];
-        DftStageGuard<LOGE, INV, 1>::run(a);
+        DftStageGuard<LOGE, INV, 1, CANON_IN>::run(a);
     }
 }
 

@@ -58,9 +58,9 @@ __device__ __noinline__ void tile_step(u64 *buf, int base, int stride, const u64
     else
     {
 #pragma unroll
-        for (int j = 0; j < E; j++) a[j] = buf[(base + j * stride) * 16];
+        for (int j = 0; j < E; j++) a[j] = gl::canon(buf[(base + j * stride) * 16]);
     }
-    dft_regs<LOGE, INV>(a);
+    dft_regs<LOGE, INV, true>(a); // a[] is canonical on both paths: the first butterfly stage skips its own canon()
     const bool scaled = out.dst != nullptr && out.post_mode != SCALE_NONE;
     if (out.dst == nullptr || scaled)
     {
