@@ -32,6 +32,23 @@ __host__ __device__ constexpr u32 mds_entry(int j, int i)
     return row0[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
 }
 
+// a*b + c folded to [0, 2^64)   (a*b + c < 2^128)
+__device__ __forceinline__ u64 mul_add_nc(u64 a, u64 b, u64 c)
+{
+    unsigned __int128 pr = (unsigned __int128)a * b + c;
+    u64 l = (u64)pr, h = (u64)(pr >> 64);
+    return gl::reduce128<false>((u32)l, (u32)(l >> 32), (u32)h, (u32)(h >> 32));
+}
+
+// x^7 + c with the round constant riding in the addend of the last product (one fold instead of a separate add)
+__device__ __forceinline__ u64 pow7_add(u64 x, u64 c)
+{
+    u64 x2 = gl::sqr_nc(x);
+    u64 x3 = gl::mul_nc(x, x2);
+    u64 x4 = gl::sqr_nc(x2);
+    return mul_add_nc(x3, x4, c);
+}
+
 __device__ __forceinline__ u64 pow7(u64 x)
 {
     u64 x2 = gl::sqr_nc(x);
@@ -167,14 +184,6 @@ struct Acc160
     }
 };
 
-// a*b + c folded to [0, 2^64)   (a*b + c < 2^128)
-__device__ __forceinline__ u64 mul_add_nc(u64 a, u64 b, u64 c)
-{
-    unsigned __int128 pr = (unsigned __int128)a * b + c;
-    u64 l = (u64)pr, h = (u64)(pr >> 64);
-    return gl::reduce128<false>((u32)l, (u32)(l >> 32), (u32)h, (u32)(h >> 32));
-}
-
 // The reference's hash_full_result on one state (poseidon_goldilocks.cpp:5-37 is the scalar statement).
 // Input words may be any 64-bit value; output words are in [0, 2^64) (callers canonicalise what they store).
 //
@@ -200,7 +209,7 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
         for (int it = 0; it < 3; it++)
         {
 #pragma unroll
-            for (int k = 0; k < 4; k++) st[k] = gl::add(pow7(st[k]), rc[4 * it + k]);
+            for (int k = 0; k < 4; k++) st[k] = pow7_add(st[k], rc[4 * it + k]);
             u64 t0 = st[0], t1 = st[1], t2 = st[2], t3 = st[3];
 #pragma unroll
             for (int k = 0; k < 8; k++) st[k] = st[k + 4];
@@ -211,7 +220,7 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
         }
 #else
 #pragma unroll
-        for (int i = 0; i < 12; i++) st[i] = gl::add(pow7(st[i]), rc[i]);
+        for (int i = 0; i < 12; i++) st[i] = pow7_add(st[i], rc[i]);
 #endif
         if (r != 3)
         {
@@ -236,7 +245,7 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
         for (int q = 0; q < 22; q++)
         {
             const u64 *S = c_S + 23 * q;
-            const u64 s0 = gl::add(pow7(st[0]), c_C[60 + q]);
+            const u64 s0 = pow7_add(st[0], c_C[60 + q]);
             Acc160 acc;
             acc.zero();
             acc.mac(s0, S[0]);
