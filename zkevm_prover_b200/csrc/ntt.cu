@@ -46,6 +46,7 @@ struct PassParams
     u64 src_ld, dst_ld;
     u64 totalQ;  // (N >> lgNp) * ncols : number of (o, r_p, column) lanes
     u32 ncols;
+    u32 ncols_inv; // floor(2^32 / ncols), 0xFFFFFFFF for ncols == 1 (ntt_tile.cuh: fastdiv)
     u32 logN;
     u32 lgM;     // log2 M_p
     u32 lgNp;    // l_p
@@ -506,6 +507,7 @@ int ntt_transform(u64 *dst, u64 dst_ld, const u64 *src, u64 src_ld, u64 *tmp, un
         P.dst = last ? dst : tmp;
         P.dst_ld = last ? dst_ld : ncols;
         P.ncols = (u32)ncols;
+        P.ncols_inv = ncols == 1 ? 0xFFFFFFFFu : (u32)(((u64)1 << 32) / ncols);
         P.logN = L;
         P.lgNp = lg[p];
         P.lgKp = consumed;

@@ -127,6 +127,20 @@ struct LaneInfo
     bool active;
 };
 
+// n / d with the host-computed M = floor(2^32 / d) (0xFFFFFFFF for d = 1): the estimate umulhi(n, M) is at most 2 short
+__device__ __forceinline__ u32 fastdiv(u32 n, u32 d, u32 M)
+{
+    u32 q = __umulhi(n, M);
+    u32 r = n - q * d;
+    if (r >= d)
+    {
+        q++;
+        r -= d;
+    }
+    if (r >= d) q++;
+    return q;
+}
+
 __device__ __forceinline__ LaneInfo decode_lane(const PassParams &P, u64 Q)
 {
     LaneInfo L;
@@ -136,12 +150,12 @@ __device__ __forceinline__ LaneInfo decode_lane(const PassParams &P, u64 Q)
     L.c = 0;
     if (L.active)
     {
-        // host guarantees totalQ < 2^32 for this kernel
+        // host guarantees totalQ < 2^32 for this kernel; lanes are numbered (o, r_p, column) with F = ncols << lgM
+        // lanes per outer index o, so o = (Q >> lgM) / ncols
         const u32 q32 = (u32)Q;
-        const u32 F = P.ncols << P.lgM;
-        const u32 o = q32 / F;
-        const u32 q = q32 - o * F;
-        L.rp = q / P.ncols;
+        const u32 o = fastdiv(q32 >> P.lgM, P.ncols, P.ncols_inv);
+        const u32 q = q32 - o * (P.ncols << P.lgM);
+        L.rp = fastdiv(q, P.ncols, P.ncols_inv);
         L.c = q - L.rp * P.ncols;
         L.o = o;
     }
