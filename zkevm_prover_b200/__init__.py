@@ -36,6 +36,7 @@ ABI_SYMBOLS = {
     "zkgpu_last_error": (ctypes.c_char_p, []),
     "zkgpu_device_count": (_int, []),
     "zkgpu_launch_count": (_u64, []),
+    "zkgpu_tune": (_int, [_int, _int]),
     "zkgpu_mem_info": (_int, [ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
     "zkgpu_malloc": (_int, [ctypes.POINTER(_vp), _u64]),
     "zkgpu_free": (_int, [_vp]),

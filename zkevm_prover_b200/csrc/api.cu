@@ -1085,6 +1085,18 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     return 0;
 }
 
+int zkgpu_tune(int key, int value)
+{
+    LOCK;
+    switch (key)
+    {
+    case 0: g_absorb_threads = value == 512 ? 512 : 128; return 0;
+    case 1: g_ntt_threads_per_sm_cap = value < 0 ? 0 : value; return 0;
+    }
+    set_error("zkgpu_tune: unknown key %d", key);
+    return -1;
+}
+
 int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t n_bits, uint64_t n_bits_ext, uint64_t n_pols)
 {
     LOCK;

@@ -403,7 +403,8 @@ static int launch_pass(const PassParams &P, bool inv, cudaStream_t st)
 }
 
 static int g_num_sms = 0;
-int g_ntt_force_v1 = 0; // test hook (ZKGPU_NTT_V1=1): always use the simple per-tile kernel
+int g_ntt_force_v1 = 0;
+int g_ntt_threads_per_sm_cap = 0; // 0: fill the SM // test hook (ZKGPU_NTT_V1=1): always use the simple per-tile kernel
 
 template <int LR1, int LR2>
 static int launch_tile(const PassParams &P, bool inv, cudaStream_t st)
@@ -428,6 +429,13 @@ static int launch_tile(const PassParams &P, bool inv, cudaStream_t st)
     }
     const u64 ntiles = (P.totalQ + 15) / 16;
     u64 grid = (u64)g_num_sms * blocks_per_sm[inv];
+    // experiment knob (zkgpu_tune key 1): leave most of each SM to another kernel
+    if (g_ntt_threads_per_sm_cap > 0)
+    {
+        u64 b = (u64)g_ntt_threads_per_sm_cap / Cfg::THREADS;
+        if (b < 1) b = 1;
+        if (b < (u64)blocks_per_sm[inv]) grid = (u64)g_num_sms * b;
+    }
     if (grid > ntiles) grid = ntiles;
     if (grid == 0) return 0;
     if (inv)

@@ -320,7 +320,8 @@ __device__ __forceinline__ void linear_hash_words(u64 (&out)[4], const u64 *__re
 // and absorbs strip_words words.  Every strip but the last must be a multiple of 8 words wide, so the chunking is the
 // one linear_hash would use on the whole row.  Lets leaf hashing follow the LDE strip by strip (and the host->device
 // copy of the next strip) instead of waiting for the whole extended trace.
-__global__ void __launch_bounds__(128) absorb_kernel(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, int first)
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) absorb_kernel(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, int first)
 {
     const u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nrows) return;
@@ -461,11 +462,19 @@ int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 
     return 0;
 }
 
+int g_absorb_threads = 128;
 int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st)
 {
     ZK_TRY(poseidon_init_constants());
     if (nrows == 0 || strip_words == 0) return 0;
-    absorb_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(leaves, rows, strip_words, row_ld, nrows, first ? 1 : 0);
+    // g_absorb_threads == 512: one 16-warp CTA per SM (two do not fit the register file), which leaves registers and
+    // shared memory for a transform CTA to run beside it.  Measured (tools/overlap_probe.py, profiles/r1_overlap_probe.txt):
+    // same sponge throughput as 128-thread CTAs, but running the LDE of the next strip beside the sponge gains only 3 %
+    // over running them back to back, so the pipeline keeps them sequential.
+    if (g_absorb_threads == 512)
+        absorb_kernel<512><<<nblocks(nrows, 512), 512, 0, st>>>(leaves, rows, strip_words, row_ld, nrows, first ? 1 : 0);
+    else
+        absorb_kernel<128><<<nblocks(nrows, 128), 128, 0, st>>>(leaves, rows, strip_words, row_ld, nrows, first ? 1 : 0);
     ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;

@@ -29,6 +29,10 @@ void set_error(const char *fmt, ...);
 extern unsigned long long g_launches;
 #define ZK_LAUNCHED() (++zk::g_launches)
 
+// ---- occupancy knobs of the overlapped commit pipeline (set by api.cu around its launches; zkgpu_tune for experiments)
+extern int g_absorb_threads;         // 128 (fill the SM) or 512 (one CTA per SM)
+extern int g_ntt_threads_per_sm_cap; // 0 = fill the SM
+
 // ---- NTT (ntt.cu) ----
 enum ScaleMode { SCALE_NONE = 0, SCALE_CONST = 1, SCALE_POWER = 2 };
 
