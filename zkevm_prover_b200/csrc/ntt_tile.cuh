@@ -163,7 +163,7 @@ __device__ __forceinline__ LaneInfo decode_lane(const PassParams &P, u64 Q)
 }
 
 template <int LR1, int LR2, bool INV>
-__global__ void __launch_bounds__(TileCfg<LR1, LR2>::THREADS, 768 / TileCfg<LR1, LR2>::THREADS) ntt_tile_kernel(const PassParams P, const u32 ntiles)
+__global__ void __launch_bounds__(TileCfg<LR1, LR2>::THREADS, 512 / TileCfg<LR1, LR2>::THREADS) ntt_tile_kernel(const PassParams P, const u32 ntiles)
 {
     using Cfg = TileCfg<LR1, LR2>;
     constexpr int R1 = Cfg::R1, R2 = Cfg::R2, R = Cfg::R, TG = Cfg::TG, THREADS = Cfg::THREADS;
