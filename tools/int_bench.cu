@@ -15,6 +15,8 @@ __global__ void __launch_bounds__(256) k(uint64_t *out, uint32_t seed, long long
     uint32_t a = threadIdx.x * 2654435761u + seed, b = a ^ 0x9e3779b9u;
     uint64_t x0 = a, x1 = b, x2 = a + 1, x3 = b + 1, x4 = a + 2, x5 = b + 2, x6 = a + 3, x7 = b + 3;
     uint32_t y0 = a, y1 = b, y2 = a + 5, y3 = b + 5, y4 = a + 6, y5 = b + 6, y6 = a + 7, y7 = b + 7;
+    double d0 = a, d1 = b, d2 = a + 1.0, d3 = b + 1.0, d4 = a + 2.0, d5 = b + 2.0, d6 = a + 3.0, d7 = b + 3.0;
+    const double dm = 1.0 + 1e-9 * (seed & 3), dc = 1e-3;
     long long t0 = clock64();
 #pragma unroll 1
     for (int i = 0; i < ITERS; i++)
@@ -90,7 +92,41 @@ __global__ void __launch_bounds__(256) k(uint64_t *out, uint32_t seed, long long
             t = gl::mul(x1, x6); x1 = gl::sub(x2, t); x2 = gl::add(x2, t);
             t = gl::mul(x3, x7); x3 = gl::sub(x0, t); x0 = gl::add(x0, t);
         }
+        else if (MODE == 9) // DFMA: 8 independent chains
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+            {
+                d0 = fma(d0, dm, dc); d1 = fma(d1, dm, dc); d2 = fma(d2, dm, dc); d3 = fma(d3, dm, dc);
+                d4 = fma(d4, dm, dc); d5 = fma(d5, dm, dc); d6 = fma(d6, dm, dc); d7 = fma(d7, dm, dc);
+            }
+        }
+        else if (MODE == 10) // 1:1 mix DFMA + IMAD.WIDE (do the two pipes run side by side?)
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+            {
+                d0 = fma(d0, dm, dc); x0 += (uint64_t)(uint32_t)x1 * b; d1 = fma(d1, dm, dc); x1 += (uint64_t)(uint32_t)x2 * b;
+                d2 = fma(d2, dm, dc); x2 += (uint64_t)(uint32_t)x3 * b; d3 = fma(d3, dm, dc); x3 += (uint64_t)(uint32_t)x0 * b;
+            }
+        }
+        else if (MODE == 11) // 2:1:1 mix DFMA + IMAD.WIDE + ALU
+        {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+            {
+                d0 = fma(d0, dm, dc); d4 = fma(d4, dm, dc); x0 += (uint64_t)(uint32_t)x1 * b; y0 = (y0 ^ y1) + a;
+                d1 = fma(d1, dm, dc); d5 = fma(d5, dm, dc); x1 += (uint64_t)(uint32_t)x0 * b; y1 = (y1 ^ y0) + a;
+            }
+        }
+        else if (MODE == 12) // I2F.F64.U32 + F2I.U64.F64 round trips (conversion pipe rate): 8 per iteration
+        {
+            y0 = (uint32_t)__double2ull_rz(__uint2double_rn(y0) + dc) ^ a; y1 = (uint32_t)__double2ull_rz(__uint2double_rn(y1) + dc) ^ a;
+            y2 = (uint32_t)__double2ull_rz(__uint2double_rn(y2) + dc) ^ a; y3 = (uint32_t)__double2ull_rz(__uint2double_rn(y3) + dc) ^ a;
+        }
     }
+    d0 += d1 + d2 + d3 + d4 + d5 + d6 + d7;
+    y0 ^= (uint32_t)__double2loint(d0);
     long long t1 = clock64();
     uint64_t s = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7 ^ y0 ^ y1 ^ y2 ^ y3 ^ y4 ^ y5 ^ y6 ^ y7;
     if (s == 0x1234567) out[0] = s;
@@ -142,6 +178,10 @@ int main()
     run<6>("gl::mul_nc (muls)", 8, out, cyc);
     run<7>("gl::mul canonical (muls)", 8, out, cyc);
     run<8>("butterfly mul+add+sub", 4, out, cyc);
+    run<9>("DFMA", 32, out, cyc);
+    run<10>("DFMA + IMAD.WIDE 16:16", 32, out, cyc);
+    run<11>("DFMA+WIDE+ALU 16:8:16", 40, out, cyc);
+    run<12>("I2F.F64+DADD+F2I.U64 x4", 12, out, cyc);
     cudaError_t e = cudaGetLastError();
     printf("status: %s\n", cudaGetErrorString(e));
     return e != cudaSuccess;

@@ -30,6 +30,9 @@ __host__ __device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi <
 
 // x = (r1:r0) + r2*(2^32-1) - r3  folded into [0, 2^64).   [hi word = r3:r2]
 // CANON: additionally x < p.
+#ifndef ZK_RED_ALU
+#define ZK_RED_ALU 0
+#endif
 template <bool CANON>
 GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
 {
@@ -54,6 +57,28 @@ GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
             : "=&r"(x0), "=&r"(x1)
             : "r"(r0), "r"(r1), "r"(r2), "r"(r3));
     }
+#if ZK_RED_ALU
+    else
+    {
+        // r2 * eps = (r2 << 32) - r2 spelled with subtract/add only: nothing for ptxas to put on the multiplier pipe
+        asm("{\n\t.reg .u32 m, c, u0, u1;\n\t"
+            "sub.cc.u32 %0, %2, %5;\n\t"
+            "subc.cc.u32 %1, %3, 0;\n\t"
+            "subc.u32 m, 0, 0;\n\t"
+            "sub.cc.u32 %0, %0, m;\n\t"
+            "subc.u32 %1, %1, 0;\n\t"
+            "sub.cc.u32 u0, 0, %4;\n\t"
+            "subc.u32 u1, %4, 0;\n\t"
+            "add.cc.u32 %0, %0, u0;\n\t"
+            "addc.cc.u32 %1, %1, u1;\n\t"
+            "addc.u32 c, 0, 0;\n\t"
+            "sub.u32 c, 0, c;\n\t"
+            "add.cc.u32 %0, %0, c;\n\t"
+            "addc.u32 %1, %1, 0;\n\t}"
+            : "=&r"(x0), "=&r"(x1)
+            : "r"(r0), "r"(r1), "r"(r2), "r"(r3));
+    }
+#else
     else
     {
         asm("{\n\t.reg .u32 m, c;\n\t"
@@ -71,6 +96,7 @@ GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
             : "=&r"(x0), "=&r"(x1)
             : "r"(r0), "r"(r1), "r"(r2), "r"(r3));
     }
+#endif
     return pack(x0, x1);
 }
 

@@ -184,6 +184,179 @@ struct Acc160
     }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// MDS on the FP64 pipe.  The MDS entries are <= 41, so with the state split in 32-bit halves every partial sum
+// sum_j M[j][i]*half_j is an integer below 2^42: exactly representable in a double.  One DFMA per matrix entry and
+// half replaces one IMAD.WIDE on the integer-multiply pipe (the pipe the S-boxes saturate), and the FP64 pipe runs
+// beside it.  B200 has a full-rate FP64 pipe (64 lanes/clk/SM); results are exact integers, there is no rounding
+// anywhere on this path.
+// ---------------------------------------------------------------------------------------------------
+#ifndef ZK_POS_FP64
+#define ZK_POS_FP64 1
+#endif
+#ifndef ZK_CONV_IN
+#define ZK_CONV_IN 1 // 0: 2^52 magic (DADD), 1: I2F.F64.U32
+#endif
+#ifndef ZK_CONV_OUT
+#define ZK_CONV_OUT 1 // 0: 2^52 magic (DADD + mask), 1: F2I.U64.F64
+#endif
+__device__ __forceinline__ double u32_to_f64(u32 x)
+{
+#if ZK_CONV_IN
+    return __uint2double_rn(x);
+#else
+    return __hiloint2double(0x43300000, (int)x) - 4503599627370496.0;
+#endif
+}
+// a is an exact integer in [0, 2^52)
+__device__ __forceinline__ u64 f64_to_u64(double a)
+{
+#if ZK_CONV_OUT
+    return __double2ull_rz(a);
+#else
+    const double t = a + 4503599627370496.0;
+    return gl::pack((u32)__double2loint(t), (u32)__double2hiint(t) & 0xFFFFFu);
+#endif
+}
+template <int I, int J>
+struct MdsDotF
+{
+    static __device__ __forceinline__ void run(double &al, double &ah, const double (&lo)[12], const double (&hi)[12])
+    {
+        constexpr double m = (double)mds_entry(J, I);
+        if (J == 0)
+        {
+            al = lo[0] * m;
+            ah = hi[0] * m;
+        }
+        else
+        {
+            al = fma(lo[J], m, al);
+            ah = fma(hi[J], m, ah);
+        }
+        MdsDotF<I, J + 1>::run(al, ah, lo, hi);
+    }
+};
+template <int I>
+struct MdsDotF<I, 12>
+{
+    static __device__ __forceinline__ void run(double &, double &, const double (&)[12], const double (&)[12]) {}
+};
+template <int I>
+struct MdsRowF
+{
+    static __device__ __forceinline__ void run(u64 (&st)[12], const double (&lo)[12], const double (&hi)[12])
+    {
+        double al, ah;
+        MdsDotF<I, 0>::run(al, ah, lo, hi);
+        st[I] = mds_combine(f64_to_u64(al), f64_to_u64(ah));
+        MdsRowF<I + 1>::run(st, lo, hi);
+    }
+};
+template <>
+struct MdsRowF<12>
+{
+    static __device__ __forceinline__ void run(u64 (&)[12], const double (&)[12], const double (&)[12]) {}
+};
+// The same product through the CRT split z^12 - 1 = prod_f (z^3 - i^f): a size-4 DFT along the stride-3 subsequences
+// (i = sqrt(-1): Gaussian integers, exact), three 3-term twisted convolutions whose constants (MDS spectrum / 4) are
+// all +-1 or powers of two — K0 = [16, 32, 16], K2 = [-1, -8, 2], K1 / 2 = [2 + i, -4 - i, 16 - i] — and the inverse
+// DFT.  78 DADD/DFMA per half-vector instead of 144 DFMA; every intermediate is an integer below 2^45.
+// y[i] = sum_j M[j][i] x[j], in place.
+__device__ __forceinline__ void mds_half_fft(double (&x)[12])
+{
+    double F0[3], F2[3], U[3], V[3];
+    const double x00 = x[0];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+    {
+        const double s02 = x[r] + x[6 + r], d02 = x[r] - x[6 + r], s13 = x[3 + r] + x[9 + r], d13 = x[3 + r] - x[9 + r];
+        F0[r] = s02 + s13;
+        F2[r] = s02 - s13;
+        U[r] = d02;
+        V[r] = d13;
+    }
+    const double T = F0[0] + F0[1] + F0[2];
+    double Y0[3], Y2[3], Re[3], Im[3];
+    Y0[0] = T + F0[2];
+    Y0[1] = T + F0[0];
+    Y0[2] = T + F0[1];
+    Y2[0] = fma(8.0, F2[2], fma(-2.0, F2[1], -F2[0]));
+    Y2[1] = fma(-8.0, F2[0], fma(-2.0, F2[2], -F2[1]));
+    Y2[2] = fma(2.0, F2[0], fma(-8.0, F2[1], -F2[2]));
+    Re[0] = fma(4.0, V[2], fma(-16.0, V[1], fma(2.0, U[0], -V[0]) + U[1]) + U[2]);
+    Im[0] = fma(-4.0, U[2], fma(16.0, U[1], fma(2.0, V[0], U[0]) + V[1]) + V[2]);
+    Re[1] = fma(-16.0, V[2], fma(2.0, U[1], fma(-4.0, U[0], V[0]) - V[1]) + U[2]);
+    Im[1] = fma(16.0, U[2], fma(2.0, V[1], fma(-4.0, V[0], -U[0]) + U[1]) + V[2]);
+    Re[2] = fma(2.0, U[2], fma(-4.0, U[1], fma(16.0, U[0], V[0]) + V[1]) - V[2]);
+    Im[2] = fma(2.0, V[2], fma(-4.0, V[1], fma(16.0, V[0], -U[0]) - U[1]) + U[2]);
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+    {
+        const double A = fma(16.0, Y0[r], Y2[r]), B = fma(16.0, Y0[r], -Y2[r]);
+        x[r] = A + Re[r];
+        x[3 + r] = B + Im[r];
+        x[6 + r] = A - Re[r];
+        x[9 + r] = B - Im[r];
+    }
+    x[0] = fma(8.0, x00, x[0]);
+}
+#ifndef ZK_MDS_FFT
+#define ZK_MDS_FFT 1
+#endif
+__device__ __forceinline__ void mds_fp64(u64 (&st)[12])
+{
+#if ZK_MDS_FFT
+    double h[12];
+    u64 al[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) h[j] = u32_to_f64((u32)st[j]);
+    mds_half_fft(h);
+#pragma unroll
+    for (int j = 0; j < 12; j++) al[j] = f64_to_u64(h[j]);
+#pragma unroll
+    for (int j = 0; j < 12; j++) h[j] = u32_to_f64((u32)(st[j] >> 32));
+    mds_half_fft(h);
+#pragma unroll
+    for (int j = 0; j < 12; j++) st[j] = mds_combine(al[j], f64_to_u64(h[j]));
+#else
+    double lo[12], hi[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++)
+    {
+        lo[j] = u32_to_f64((u32)st[j]);
+        hi[j] = u32_to_f64((u32)(st[j] >> 32));
+    }
+    MdsRowF<0>::run(st, lo, hi);
+#endif
+}
+
+#if ZK_POS_FP64
+// Dense form of the same permutation.  The reference's sparse partial rounds (matrices P and S) are an algebraic
+// refactoring of "x0 <- x0^7 + k_q ; x <- MDS x" made for CPUs, where a full 64x64 multiply costs one instruction and
+// 23 of them beat 144 small-constant products.  Here the small-constant products ride the FP64 pipe, so the dense form
+// (same scalar constants C[60+q], plain MDS in place of P and of every S_q: S_q = B_{q+1}^-1 M B_q with block-diagonal
+// B that commute with the x0 S-box, P = B_0^-1 M, B_22 = I) costs 4 integer multiplies per partial round instead of 27.
+// All 30 rounds share one loop body; outputs are word-for-word those of the sparse form (tests/test_gpu_parity.py).
+__device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
+{
+#pragma unroll
+    for (int i = 0; i < 12; i++) st[i] = gl::add(st[i], c_C[i]);
+#pragma unroll 1
+    for (int r = 0; r < 30; r++)
+    {
+        if (r < 4 || r >= 26)
+        {
+            const u64 *rc = c_RC + (r < 4 ? r : r - 22) * 12;
+#pragma unroll
+            for (int i = 0; i < 12; i++) st[i] = pow7_add(st[i], rc[i]);
+        }
+        else
+            st[0] = pow7_add(st[0], c_C[56 + r]); // C[60 + q], q = r - 4
+        mds_fp64(st);
+    }
+}
+#else
 // The reference's hash_full_result on one state (poseidon_goldilocks.cpp:5-37 is the scalar statement).
 // Input words may be any 64-bit value; output words are in [0, 2^64) (callers canonicalise what they store).
 //
@@ -257,6 +430,8 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
         }
     }
 }
+
+#endif // ZK_POS_FP64
 
 // ---------------------------------------------------------------------------------------------------
 // kernels
