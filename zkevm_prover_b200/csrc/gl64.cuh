@@ -30,6 +30,16 @@ __host__ __device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi <
 
 // x = (r1:r0) + r2*(2^32-1) - r3  folded into [0, 2^64).   [hi word = r3:r2]
 // CANON: additionally x < p.
+// 0/1 carry -> 0/0xFFFFFFFF mask.  bfe.s32 (SGXT, ALU pipe) keeps the negation off the multiplier pipe, where ptxas
+// would otherwise place it as IMAD.MOV.
+#ifndef ZK_MASK_BFE
+#define ZK_MASK_BFE 0
+#endif
+#if ZK_MASK_BFE
+#define ZK_NEG_MASK "bfe.s32 c, c, 0, 1;\n\t"
+#else
+#define ZK_NEG_MASK "sub.u32 c, 0, c;\n\t"
+#endif
 #ifndef ZK_RED_ALU
 #define ZK_RED_ALU 0
 #endif
@@ -72,7 +82,7 @@ GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
             "add.cc.u32 %0, %0, u0;\n\t"
             "addc.cc.u32 %1, %1, u1;\n\t"
             "addc.u32 c, 0, 0;\n\t"
-            "sub.u32 c, 0, c;\n\t"
+            ZK_NEG_MASK
             "add.cc.u32 %0, %0, c;\n\t"
             "addc.u32 %1, %1, 0;\n\t}"
             : "=&r"(x0), "=&r"(x1)
@@ -90,7 +100,7 @@ GL_DEV u64 reduce128(u32 r0, u32 r1, u32 r2, u32 r3)
             "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t"
             "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
             "addc.u32 c, 0, 0;\n\t"
-            "sub.u32 c, 0, c;\n\t"         // mask
+            ZK_NEG_MASK
             "add.cc.u32 %0, %0, c;\n\t"    // r += eps when carry
             "addc.u32 %1, %1, 0;\n\t}"
             : "=&r"(x0), "=&r"(x1)
@@ -109,7 +119,27 @@ GL_DEV u64 mul_t(u64 a, u64 b)
 }
 GL_DEV u64 mul(u64 a, u64 b) { return mul_t<true>(a, b); }
 GL_DEV u64 mul_nc(u64 a, u64 b) { return mul_t<false>(a, b); }
+#ifndef ZK_SQR3
+#define ZK_SQR3 0
+#endif
+#if ZK_SQR3
+// a^2 with three products: a0^2 + 2 a0 a1 2^32 + a1^2 2^64; the doubling is a funnel shift (ALU pipe)
+GL_DEV u64 sqr_nc(u64 a)
+{
+    const u32 a0 = (u32)a, a1 = (u32)(a >> 32);
+    const u64 p0 = (u64)a0 * a0, p1 = (u64)a0 * a1, p3 = (u64)a1 * a1;
+    const u32 d0 = (u32)p1 << 1, d1 = __funnelshift_l((u32)p1, (u32)(p1 >> 32), 1), d2 = (u32)(p1 >> 63);
+    u32 r1, r2, r3;
+    asm("add.cc.u32 %0, %3, %4;\n\t"
+        "addc.cc.u32 %1, %5, %6;\n\t"
+        "addc.u32 %2, %7, %8;"
+        : "=r"(r1), "=&r"(r2), "=&r"(r3)
+        : "r"((u32)(p0 >> 32)), "r"(d0), "r"((u32)p3), "r"(d1), "r"((u32)(p3 >> 32)), "r"(d2));
+    return reduce128<false>((u32)p0, r1, r2, r3);
+}
+#else
 GL_DEV u64 sqr_nc(u64 a) { return mul_t<false>(a, a); }
+#endif
 
 // a + b, requires min(a,b) < p (then a single 2^64 -> eps fold cannot overflow again)
 GL_DEV u64 add(u64 a, u64 b)
@@ -119,7 +149,7 @@ GL_DEV u64 add(u64 a, u64 b)
         "add.cc.u32 %0, %2, %4;\n\t"
         "addc.cc.u32 %1, %3, %5;\n\t"
         "addc.u32 c, 0, 0;\n\t"
-        "sub.u32 c, 0, c;\n\t"
+        ZK_NEG_MASK
         "add.cc.u32 %0, %0, c;\n\t"
         "addc.u32 %1, %1, 0;\n\t}"
         : "=&r"(s0), "=&r"(s1)

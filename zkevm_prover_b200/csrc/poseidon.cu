@@ -65,7 +65,7 @@ __device__ __forceinline__ u64 fold96(u32 r0, u32 r1, u32 r2)
         "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %2;\n\t"
         "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %3;\n\t"
         "addc.u32 c, 0, 0;\n\t"
-        "sub.u32 c, 0, c;\n\t"
+        ZK_NEG_MASK
         "add.cc.u32 %0, %0, c;\n\t"
         "addc.u32 %1, %1, 0;\n\t}"
         : "=&r"(x0), "=&r"(x1)
@@ -263,43 +263,64 @@ struct MdsRowF<12>
 // all +-1 or powers of two — K0 = [16, 32, 16], K2 = [-1, -8, 2], K1 / 2 = [2 + i, -4 - i, 16 - i] — and the inverse
 // DFT.  78 DADD/DFMA per half-vector instead of 144 DFMA; every intermediate is an integer below 2^45.
 // y[i] = sum_j M[j][i] x[j], in place.
+struct Spectrum
+{
+    double f0[3], f2[3], u[3], v[3]; // z^3-1 block, z^3+1 block, real and imaginary part of the z^3-i block
+};
+__device__ __forceinline__ void mds_dft(Spectrum &s, const double (&x)[12])
+{
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+    {
+        const double s02 = x[r] + x[6 + r], s13 = x[3 + r] + x[9 + r];
+        s.u[r] = x[r] - x[6 + r];
+        s.v[r] = x[3 + r] - x[9 + r];
+        s.f0[r] = s02 + s13;
+        s.f2[r] = s02 - s13;
+    }
+}
+// the three twisted 3-term convolutions, in place; f0 comes out divided by 16 (mds_idft multiplies it back)
+__device__ __forceinline__ void mds_blocks(Spectrum &s)
+{
+    const double T = s.f0[0] + s.f0[1] + s.f0[2];
+    const double a0 = s.f0[0], a1 = s.f0[1], a2 = s.f0[2];
+    s.f0[0] = T + a2;
+    s.f0[1] = T + a0;
+    s.f0[2] = T + a1;
+    const double b0 = s.f2[0], b1 = s.f2[1], b2 = s.f2[2];
+    s.f2[0] = fma(8.0, b2, fma(-2.0, b1, -b0));
+    s.f2[1] = fma(-8.0, b0, fma(-2.0, b2, -b1));
+    s.f2[2] = fma(2.0, b0, fma(-8.0, b1, -b2));
+    const double U0 = s.u[0], U1 = s.u[1], U2 = s.u[2], V0 = s.v[0], V1 = s.v[1], V2 = s.v[2];
+    s.u[0] = fma(4.0, V2, fma(-16.0, V1, fma(2.0, U0, -V0) + U1) + U2);
+    s.v[0] = fma(-4.0, U2, fma(16.0, U1, fma(2.0, V0, U0) + V1) + V2);
+    s.u[1] = fma(-16.0, V2, fma(2.0, U1, fma(-4.0, U0, V0) - V1) + U2);
+    s.v[1] = fma(16.0, U2, fma(2.0, V1, fma(-4.0, V0, -U0) + U1) + V2);
+    s.u[2] = fma(2.0, U2, fma(-4.0, U1, fma(16.0, U0, V0) + V1) - V2);
+    s.v[2] = fma(2.0, V2, fma(-4.0, V1, fma(16.0, V0, -U0) - U1) + U2);
+}
+// x[3k + r] = C0 f0[r] + (-1)^k f2[r] + C1 Re((u[r] + i v[r]) (-i)^k);  then the diagonal term 8 x0 on word 0
+template <int C0, int C1>
+__device__ __forceinline__ void mds_idft(double (&x)[12], const Spectrum &s, double x0)
+{
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+    {
+        const double A = fma((double)C0, s.f0[r], s.f2[r]), B = fma((double)C0, s.f0[r], -s.f2[r]);
+        x[r] = fma((double)C1, s.u[r], A);
+        x[3 + r] = fma((double)C1, s.v[r], B);
+        x[6 + r] = fma((double)-C1, s.u[r], A);
+        x[9 + r] = fma((double)-C1, s.v[r], B);
+    }
+    x[0] = fma(8.0, x0, x[0]);
+}
 __device__ __forceinline__ void mds_half_fft(double (&x)[12])
 {
-    double F0[3], F2[3], U[3], V[3];
-    const double x00 = x[0];
-#pragma unroll
-    for (int r = 0; r < 3; r++)
-    {
-        const double s02 = x[r] + x[6 + r], d02 = x[r] - x[6 + r], s13 = x[3 + r] + x[9 + r], d13 = x[3 + r] - x[9 + r];
-        F0[r] = s02 + s13;
-        F2[r] = s02 - s13;
-        U[r] = d02;
-        V[r] = d13;
-    }
-    const double T = F0[0] + F0[1] + F0[2];
-    double Y0[3], Y2[3], Re[3], Im[3];
-    Y0[0] = T + F0[2];
-    Y0[1] = T + F0[0];
-    Y0[2] = T + F0[1];
-    Y2[0] = fma(8.0, F2[2], fma(-2.0, F2[1], -F2[0]));
-    Y2[1] = fma(-8.0, F2[0], fma(-2.0, F2[2], -F2[1]));
-    Y2[2] = fma(2.0, F2[0], fma(-8.0, F2[1], -F2[2]));
-    Re[0] = fma(4.0, V[2], fma(-16.0, V[1], fma(2.0, U[0], -V[0]) + U[1]) + U[2]);
-    Im[0] = fma(-4.0, U[2], fma(16.0, U[1], fma(2.0, V[0], U[0]) + V[1]) + V[2]);
-    Re[1] = fma(-16.0, V[2], fma(2.0, U[1], fma(-4.0, U[0], V[0]) - V[1]) + U[2]);
-    Im[1] = fma(16.0, U[2], fma(2.0, V[1], fma(-4.0, V[0], -U[0]) + U[1]) + V[2]);
-    Re[2] = fma(2.0, U[2], fma(-4.0, U[1], fma(16.0, U[0], V[0]) + V[1]) - V[2]);
-    Im[2] = fma(2.0, V[2], fma(-4.0, V[1], fma(16.0, V[0], -U[0]) - U[1]) + U[2]);
-#pragma unroll
-    for (int r = 0; r < 3; r++)
-    {
-        const double A = fma(16.0, Y0[r], Y2[r]), B = fma(16.0, Y0[r], -Y2[r]);
-        x[r] = A + Re[r];
-        x[3 + r] = B + Im[r];
-        x[6 + r] = A - Re[r];
-        x[9 + r] = B - Im[r];
-    }
-    x[0] = fma(8.0, x00, x[0]);
+    Spectrum s;
+    const double x0 = x[0];
+    mds_dft(s, x);
+    mds_blocks(s);
+    mds_idft<16, 1>(x, s, x0);
 }
 #ifndef ZK_MDS_FFT
 #define ZK_MDS_FFT 1
@@ -338,6 +359,98 @@ __device__ __forceinline__ void mds_fp64(u64 (&st)[12])
 // (same scalar constants C[60+q], plain MDS in place of P and of every S_q: S_q = B_{q+1}^-1 M B_q with block-diagonal
 // B that commute with the x0 S-box, P = B_0^-1 M, B_22 = I) costs 4 integer multiplies per partial round instead of 27.
 // All 30 rounds share one loop body; outputs are word-for-word those of the sparse form (tests/test_gpu_parity.py).
+#ifndef ZK_LAZY2
+#define ZK_LAZY2 2
+#endif
+#if ZK_LAZY2
+// Partial rounds go in pairs: the eleven words that skip the S-box stay in the FP domain between the two MDS products
+// of a pair (halves grow 32 -> 41 -> 49 bits, still exact in a double), only word 0 makes the trip to the integer
+// side for its S-box.  Saves 44 conversions and 11 recombinations per pair.
+__device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
+{
+#pragma unroll
+    for (int i = 0; i < 12; i++) st[i] = gl::add(st[i], c_C[i]);
+#pragma unroll 1
+    for (int it = 0; it < 19; it++)
+    {
+        if (it < 4 || it >= 15)
+        {
+            const u64 *rc = c_RC + (it < 4 ? it : it - 11) * 12;
+#pragma unroll
+            for (int i = 0; i < 12; i++) st[i] = pow7_add(st[i], rc[i]);
+            mds_fp64(st);
+            continue;
+        }
+        const u64 *k = c_C + 60 + 2 * (it - 4);
+        st[0] = pow7_add(st[0], k[0]);
+#if ZK_LAZY2 == 2
+        // ... and between the two products the state stays in the DFT domain as well: the inverse transform of the
+        // first product and the forward transform of the second cancel up to powers of two (the DFT of the inverse
+        // DFT of (f0, f2, u + iv) is (64 f0, 4 f2, 2 (u + iv)) in the scaling mds_blocks leaves), and replacing word 0
+        // by its S-box image adds d = new - old to f0[0], f2[0] and u[0].
+        Spectrum sl, sh;
+        double h[12];
+#pragma unroll
+        for (int j = 0; j < 12; j++) h[j] = u32_to_f64((u32)st[j]);
+        mds_dft(sl, h);
+        mds_blocks(sl);
+        const double yl = fma(16.0, sl.f0[0], sl.f2[0]) + sl.u[0]; // word 0 of the circulant part
+        const double wl = fma(8.0, h[0], yl);
+#pragma unroll
+        for (int j = 0; j < 12; j++) h[j] = u32_to_f64((u32)(st[j] >> 32));
+        mds_dft(sh, h);
+        mds_blocks(sh);
+        const double yh = fma(16.0, sh.f0[0], sh.f2[0]) + sh.u[0];
+        const double wh = fma(8.0, h[0], yh);
+        const u64 w0 = pow7_add(mds_combine(f64_to_u64(wl), f64_to_u64(wh)), k[1]);
+        const double xl = u32_to_f64((u32)w0), xh = u32_to_f64((u32)(w0 >> 32));
+        {
+            const double d = xl - yl;
+            sl.f0[0] = fma(d, 0.015625, sl.f0[0]);
+            sl.f2[0] = fma(4.0, sl.f2[0], d);
+            sl.f2[1] *= 4.0;
+            sl.f2[2] *= 4.0;
+            sl.u[0] = fma(d, 0.5, sl.u[0]);
+        }
+        mds_blocks(sl);
+        mds_idft<1024, 2>(h, sl, xl);
+        u64 al[12];
+#pragma unroll
+        for (int j = 0; j < 12; j++) al[j] = f64_to_u64(h[j]);
+        {
+            const double d = xh - yh;
+            sh.f0[0] = fma(d, 0.015625, sh.f0[0]);
+            sh.f2[0] = fma(4.0, sh.f2[0], d);
+            sh.f2[1] *= 4.0;
+            sh.f2[2] *= 4.0;
+            sh.u[0] = fma(d, 0.5, sh.u[0]);
+        }
+        mds_blocks(sh);
+        mds_idft<1024, 2>(h, sh, xh);
+#pragma unroll
+        for (int j = 0; j < 12; j++) st[j] = mds_combine(al[j], f64_to_u64(h[j]));
+#else
+        double hl[12], hh[12];
+#pragma unroll
+        for (int j = 0; j < 12; j++) hl[j] = u32_to_f64((u32)st[j]);
+        mds_half_fft(hl);
+#pragma unroll
+        for (int j = 0; j < 12; j++) hh[j] = u32_to_f64((u32)(st[j] >> 32));
+        mds_half_fft(hh);
+        const u64 w0 = pow7_add(mds_combine(f64_to_u64(hl[0]), f64_to_u64(hh[0])), k[1]);
+        hl[0] = u32_to_f64((u32)w0);
+        hh[0] = u32_to_f64((u32)(w0 >> 32));
+        mds_half_fft(hl);
+        u64 al[12];
+#pragma unroll
+        for (int j = 0; j < 12; j++) al[j] = f64_to_u64(hl[j]);
+        mds_half_fft(hh);
+#pragma unroll
+        for (int j = 0; j < 12; j++) st[j] = mds_combine(al[j], f64_to_u64(hh[j]));
+#endif
+    }
+}
+#else
 __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
 {
 #pragma unroll
@@ -356,6 +469,7 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
         mds_fp64(st);
     }
 }
+#endif // ZK_LAZY2
 #else
 // The reference's hash_full_result on one state (poseidon_goldilocks.cpp:5-37 is the scalar statement).
 // Input words may be any 64-bit value; output words are in [0, 2^64) (callers canonicalise what they store).
