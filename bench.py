@@ -339,8 +339,9 @@ def run_ours(args):
                 "unit": "GB/s", "frac": achieved / peak_gbs if achieved else None, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": leaf_bytes,
                 "permutations_per_s": (n_ext * (-(-c // 8)) / world) / (leaf_ms * 1e-3) if leaf_ms else None,
-                "note": "integer-pipe bound kernel (about 1.4e9 Poseidon permutations per step, 26k SASS instructions each, "
-                        "running at the measured 64-bit modmul chain rate of the SM: profiles/r1_int_bench.txt); HBM fraction is low by nature"}
+                "note": "arithmetic-bound kernel (about 1.4e9 Poseidon permutations per step: 472 64-bit modular multiplies on the "
+                        "integer-multiply pipe + 30 MDS products on the FP64 pipe each; the two pipes share a dispatch port that ncu "
+                        "shows 95 % busy: profiles/r1_ncu_quick_poseidon_fp64.txt); HBM fraction is low by nature"}
     lde_ms = stages.get("lde")
     lde_bytes = 8 * c * (n + n_ext) / world
     roofline_lde = {"stage": "extendPol (INTT + coset NTTs, all passes)", "bound": "hbm",
