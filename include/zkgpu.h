@@ -127,6 +127,10 @@ int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_wor
  * Every strip of a row but the last must be a multiple of 8 words; after the last strip leaves[] holds
  * linear_hash(row) for rows longer than 4 words. */
 int zkgpu_merkle_absorb(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t num_rows, int first);
+/* the same, and the words absorbed are also stored at copy_to + i*copy_ld (assembles the row-major extended trace that
+ * MerkleTreeGL::source points at, merkleTreeGL.hpp:18-28, from exchanged column pieces without a separate copy pass) */
+int zkgpu_merkle_absorb_copy(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t num_rows, int first,
+                             uint64_t *copy_to, uint64_t copy_ld);
 /* node levels above num_rows leaves already stored at tree[0 .. 4*num_rows) (poseidon_goldilocks.cpp:283-300) */
 int zkgpu_merkle_levels(uint64_t *tree, uint64_t num_rows);
 /* gather/scatter between a row-major matrix and a packed block: dst[r*ncols + c] = src[(row0 + r)*src_ld + col0 + c]

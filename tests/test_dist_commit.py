@@ -40,9 +40,11 @@ class OracleOps:
         t = self.O.merkletree(self._np(rows)[:nrows * ncols].copy(), ncols, nrows)
         self._np(tree)[:nrows * 4] = t[:nrows * 4]
 
-    def absorb(self, leaves, block, block_off, width, ld, nrows, first):
+    def absorb(self, leaves, block, block_off, width, ld, nrows, first, copy_to=None, copy_off=0, copy_ld=0):
         # running digest after a whole number of 8-word blocks == linear_hash of the row prefix absorbed so far
         blk = self._np(block)[block_off: block_off + nrows * ld].reshape(nrows, ld)[:, :width]
+        if copy_to is not None:
+            self.copy_block(copy_to, copy_off, copy_ld, block, block_off, ld, nrows, width)
         self.prefix = blk.copy() if first else np.concatenate([self.prefix, blk], axis=1)
         w = self.prefix.shape[1]
         t = self.O.merkletree(np.ascontiguousarray(self.prefix).reshape(-1), w, nrows)

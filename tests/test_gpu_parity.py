@@ -470,3 +470,35 @@ def test_adversarial_value_sets():
             want = O.extend_pol(a, n * b)
             assert_eq(ext, want, "%s c=%d ext" % (name, c))
             assert_eq(tree, O.merkletree(want, c, n * b), "%s c=%d tree" % (name, c))
+
+
+def test_sharded_building_blocks_absorb_copy():
+    """The multi-GPU building blocks on one device (GpuOps, dist_commit.py): the row sponge fed piece by piece, with
+    the fused scatter of each piece into the row-major matrix, equals linear_hash of the assembled rows; ragged last
+    piece, 8-aligned pieces before it."""
+    import torch
+    from zkevm_prover_b200.dist_commit import GpuOps
+    ops = GpuOps()
+    rows, widths = 4096, [16, 24, 8, 13]
+    ncols = sum(widths)
+    a = O.fill(rows * ncols, SEED, 5).reshape(rows, ncols)
+    leaves = torch.zeros(rows * 4, dtype=torch.int64, device="cuda")
+    full = torch.zeros(rows * ncols, dtype=torch.int64, device="cuda")
+    c0 = 0
+    for i, w in enumerate(widths):
+        piece = torch.from_numpy(np.ascontiguousarray(a[:, c0:c0 + w]).view(np.int64).reshape(-1)).cuda()
+        torch.cuda.synchronize()  # the library enqueues on its own stream
+        ops.absorb(leaves, piece, 0, w, w, rows, i == 0, full, c0, ncols)
+        zk.sync()
+        c0 += w
+    assert_eq(_host(full), a, "scattered rows")
+    assert_eq(_host(leaves), O.merkletree(a.reshape(-1), ncols, rows)[:rows * 4], "leaf digests")
+    # without the copy the digests are the same
+    leaves2 = torch.zeros(rows * 4, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    c0 = 0
+    for i, w in enumerate(widths):
+        ops.absorb(leaves2, full, c0, w, ncols, rows, i == 0)
+        c0 += w
+    zk.sync()
+    assert_eq(_host(leaves2), _host(leaves), "absorb without copy")

@@ -61,6 +61,7 @@ ABI_SYMBOLS = {
     "zkgpu_lde_columns": (_int, [_vp, _u64, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_merkle_leaves": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_merkle_absorb": (_int, [_vp, _vp, _u64, _u64, _u64, _int]),
+    "zkgpu_merkle_absorb_copy": (_int, [_vp, _vp, _u64, _u64, _u64, _int, _vp, _u64]),
     "zkgpu_merkle_levels": (_int, [_vp, _u64]),
     "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
 }

@@ -985,6 +985,18 @@ int zkgpu_merkle_absorb(uint64_t *leaves, const uint64_t *rows, uint64_t strip_w
     NEED_CTX;
     return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, g_ctx.cur);
 }
+int zkgpu_merkle_absorb_copy(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t nrows, int first,
+                             uint64_t *copy_to, uint64_t copy_ld)
+{
+    LOCK;
+    NEED_CTX;
+    if (!copy_to)
+    {
+        set_error("merkle_absorb_copy: null destination");
+        return -1;
+    }
+    return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, g_ctx.cur, copy_to, copy_ld);
+}
 int zkgpu_merkle_levels(uint64_t *tree, uint64_t nrows)
 {
     LOCK;

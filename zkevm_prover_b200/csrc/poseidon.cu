@@ -564,7 +564,10 @@ __global__ void __launch_bounds__(128) permute_kernel(u64 *out, const u64 *in, u
 
 // sponge absorption of `count` (>= 1) words at p, rate 8, starting from capacity st[8..11]; on return st[0..3] is the
 // running digest (un-normalised).  The last chunk is zero padded (poseidon_goldilocks.cpp:244-256).
-__device__ __forceinline__ void sponge_absorb(u64 (&st)[12], const u64 *__restrict__ p, u64 count)
+// COPY: the words are also written to q[0..count) as they are read (the multi-GPU path assembles the row-major
+// extended trace from the exchanged pieces this way instead of with a separate copy pass).
+template <bool COPY = false>
+__device__ __forceinline__ void sponge_absorb(u64 (&st)[12], const u64 *__restrict__ p, u64 count, u64 *__restrict__ q = nullptr)
 {
     u64 done = 0;
     while (done < count)
@@ -574,11 +577,22 @@ __device__ __forceinline__ void sponge_absorb(u64 (&st)[12], const u64 *__restri
         {
 #pragma unroll
             for (int i = 0; i < 8; i++) st[i] = p[done + i];
+            if (COPY)
+            {
+#pragma unroll
+                for (int i = 0; i < 8; i++) q[done + i] = st[i];
+            }
         }
         else
         {
 #pragma unroll
             for (int i = 0; i < 8; i++) st[i] = (u64)i < n ? p[done + i] : 0;
+            if (COPY)
+            {
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    if ((u64)i < n) q[done + i] = st[i];
+            }
         }
         poseidon_permute_state(st);
         done += n;
@@ -609,8 +623,9 @@ __device__ __forceinline__ void linear_hash_words(u64 (&out)[4], const u64 *__re
 // and absorbs strip_words words.  Every strip but the last must be a multiple of 8 words wide, so the chunking is the
 // one linear_hash would use on the whole row.  Lets leaf hashing follow the LDE strip by strip (and the host->device
 // copy of the next strip) instead of waiting for the whole extended trace.
-template <int THREADS>
-__global__ void __launch_bounds__(THREADS) absorb_kernel(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, int first)
+template <int THREADS, bool COPY = false>
+__global__ void __launch_bounds__(THREADS) absorb_kernel(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, int first,
+                                                         u64 *copy_to = nullptr, u64 copy_ld = 0)
 {
     const u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nrows) return;
@@ -629,7 +644,7 @@ __global__ void __launch_bounds__(THREADS) absorb_kernel(u64 *leaves, const u64 
         st[10] = b.x;
         st[11] = b.y;
     }
-    sponge_absorb(st, rows + row * row_ld, strip_words);
+    sponge_absorb<COPY>(st, rows + row * row_ld, strip_words, COPY ? copy_to + row * copy_ld : nullptr);
     o[0] = make_ulonglong2(gl::canon(st[0]), gl::canon(st[1]));
     o[1] = make_ulonglong2(gl::canon(st[2]), gl::canon(st[3]));
 }
@@ -752,10 +767,18 @@ int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 
 }
 
 int g_absorb_threads = 128;
-int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st)
+int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st, u64 *copy_to,
+                  u64 copy_ld)
 {
     ZK_TRY(poseidon_init_constants());
     if (nrows == 0 || strip_words == 0) return 0;
+    if (copy_to)
+    {
+        absorb_kernel<128, true><<<nblocks(nrows, 128), 128, 0, st>>>(leaves, rows, strip_words, row_ld, nrows, first ? 1 : 0, copy_to, copy_ld);
+        ZK_LAUNCHED();
+        ZK_CUDA(cudaGetLastError());
+        return 0;
+    }
     // g_absorb_threads == 512: one 16-warp CTA per SM (two do not fit the register file), which leaves registers and
     // shared memory for a transform CTA to run beside it.  Measured (tools/overlap_probe.py, profiles/r1_overlap_probe.txt):
     // same sponge throughput as 128-thread CTAs, but running the LDE of the next strip beside the sponge gains only 3 %

@@ -68,7 +68,8 @@ int poseidon_init_constants();
 int merkle_leaves(u64 *leaves, const u64 *input, u64 row_words, u64 row_ld, u64 nrows, cudaStream_t st);
 // one column strip of the row sponge (strip_words a multiple of 8 except for the last strip of a row); the running
 // digest lives in leaves[4*i .. 4*i+3]
-int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st);
+int merkle_absorb(u64 *leaves, const u64 *rows, u64 strip_words, u64 row_ld, u64 nrows, bool first, cudaStream_t st, u64 *copy_to = nullptr,
+                  u64 copy_ld = 0);
 // two-level (batched) leaves: PoseidonGoldilocks::merkletree_batch semantics
 int merkle_leaves_batch(u64 *leaves, const u64 *input, u64 ncols, u64 dim, u64 batch, u64 nrows, cudaStream_t st);
 // all node levels above nrows leaves stored at tree[0 .. 4*nrows): reference level-major layout

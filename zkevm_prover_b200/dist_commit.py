@@ -59,8 +59,13 @@ class GpuOps:
     def levels(self, tree, nleaves, word_off=0):
         self.zk._check(self.zk.lib().zkgpu_merkle_levels(tree.data_ptr() + 8 * word_off, nleaves))
 
-    def absorb(self, leaves, block, block_off, width, ld, nrows, first):
-        self.zk._check(self.zk.lib().zkgpu_merkle_absorb(leaves.data_ptr(), block.data_ptr() + 8 * block_off, width, ld, nrows, int(first)))
+    def absorb(self, leaves, block, block_off, width, ld, nrows, first, copy_to=None, copy_off=0, copy_ld=0):
+        """Row sponge over one column piece; with copy_to the piece is also scattered into the row-major matrix."""
+        if copy_to is None:
+            self.zk._check(self.zk.lib().zkgpu_merkle_absorb(leaves.data_ptr(), block.data_ptr() + 8 * block_off, width, ld, nrows, int(first)))
+        else:
+            self.zk._check(self.zk.lib().zkgpu_merkle_absorb_copy(leaves.data_ptr(), block.data_ptr() + 8 * block_off, width, ld, nrows,
+                                                                   int(first), copy_to.data_ptr() + 8 * copy_off, copy_ld))
 
     # ---- host -> device staging of input pieces on a copy stream (two slots), used by commit_sharded_pipelined
     def stage(self, src, slot):
@@ -182,8 +187,7 @@ def commit_sharded_pipelined(ops, dist, pieces_in, n, n_ext, ncols, rounds=None,
         for g in range(world):
             c0, w = plan[k][g]
             if w:
-                ops.absorb(sub, recv, off, w, w, R, k == 0 and g == 0)
-                ops.copy_block(rows, c0, ncols, recv, off, w, R, w)
+                ops.absorb(sub, recv, off, w, w, R, k == 0 and g == 0, rows, c0, ncols)
             off += R * w
         mark("leaves")
 
