@@ -320,3 +320,65 @@ void oracle_fill(u64 *x, u64 n, u64 seed, u64 offset)
 #pragma omp parallel for
     for (u64 i = 0; i < n; i++) x[i] = splitmix64(seed + offset + i) % GL_P;
 }
+
+/* ---------------- FRI folding step (src/starkpil/fri/friProve.cpp:26-107) ----------------
+ * Elements of the cubic extension F_p[x]/(x^3 - x - 1) are 3 consecutive words.
+ * Polinomial::mulElement, dim 3 x dim 3 (src/starkpil/polinomial.hpp:193-206). */
+static void gl3_mul(u64 *o, const u64 *a, const u64 *b)
+{
+    u64 A = gl_mul(gl_add(a[0], a[1]), gl_add(b[0], b[1]));
+    u64 B = gl_mul(gl_add(a[0], a[2]), gl_add(b[0], b[2]));
+    u64 C = gl_mul(gl_add(a[1], a[2]), gl_add(b[1], b[2]));
+    u64 D = gl_mul(a[0], b[0]), E = gl_mul(a[1], b[1]), F = gl_mul(a[2], b[2]);
+    u64 G = gl_sub(D, E);
+    u64 o0 = gl_sub(gl_add(C, G), F);
+    u64 o1 = gl_sub(gl_sub(gl_sub(gl_add(A, C), E), E), D);
+    u64 o2 = gl_sub(B, G);
+    o[0] = o0; o[1] = o1; o[2] = o2;
+}
+
+/* One folding step for si > 0: for every g < pol2N = 2^next_bits
+ *   ppar[i] = friPol[i*pol2N + g], i < nX = 2^(pol_bits - next_bits)          (friProve.cpp:95-98)
+ *   ppar_c = INTT_nX(ppar)                                                      (:99-101)
+ *   ppar_c[i] *= sinv_g^i, sinv_g = shiftInv * w(polBits)^(-g)  (polMulAxi :192-200; sinv walk :36, :64-81, :105)
+ *   pol2_e[g] = ppar_c evaluated at special_x by Horner                        (evalPol :201-217)
+ * out: pol2N x 3 words. */
+void oracle_fri_fold(u64 *pol2_e, const u64 *fri_pol, u64 pol_bits, u64 next_bits, u64 shift_inv, const u64 *special_x)
+{
+    const u64 pol2n = (u64)1 << next_bits, nx = (u64)1 << (pol_bits - next_bits);
+    const u64 wi = gl_inv(gl_w((unsigned)pol_bits));
+    u64 *ppar = (u64 *)malloc(nx * 3 * sizeof(u64)), *ppar_c = (u64 *)malloc(nx * 3 * sizeof(u64));
+    u64 sinv = shift_inv;
+    for (u64 g = 0; g < pol2n; g++)
+    {
+        for (u64 i = 0; i < nx; i++)
+            for (int k = 0; k < 3; k++) ppar[i * 3 + k] = fri_pol[(i * pol2n + g) * 3 + k];
+        oracle_intt(ppar_c, ppar, nx, 3, 0);
+        u64 r = 1;
+        for (u64 i = 0; i < nx; i++)
+        {
+            for (int k = 0; k < 3; k++) ppar_c[i * 3 + k] = gl_mul(ppar_c[i * 3 + k], r);
+            r = gl_mul(r, sinv);
+        }
+        u64 res[3] = {ppar_c[(nx - 1) * 3], ppar_c[(nx - 1) * 3 + 1], ppar_c[(nx - 1) * 3 + 2]};
+        for (u64 i = nx - 1; i-- > 0;)
+        {
+            u64 aux[3];
+            gl3_mul(aux, res, special_x);
+            for (int k = 0; k < 3; k++) res[k] = gl_add(aux[k], ppar_c[i * 3 + k]);
+        }
+        for (int k = 0; k < 3; k++) pol2_e[g * 3 + k] = res[k];
+        sinv = gl_mul(sinv, wi);
+    }
+    free(ppar);
+    free(ppar_c);
+}
+
+/* FRIProve::getTransposed (friProve.cpp:252-271): aux[i*h + j] = pol[j*w + i], w = 2^transpose_bits, h = degree / w */
+void oracle_fri_transpose(u64 *aux, const u64 *pol, u64 degree, u64 transpose_bits)
+{
+    const u64 w = (u64)1 << transpose_bits, h = degree / w;
+    for (u64 i = 0; i < w; i++)
+        for (u64 j = 0; j < h; j++)
+            for (int k = 0; k < 3; k++) aux[(i * h + j) * 3 + k] = pol[(j * w + i) * 3 + k];
+}

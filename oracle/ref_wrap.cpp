@@ -6,10 +6,19 @@
 #include "goldilocks_base_field.hpp"
 #include "ntt_goldilocks.hpp"
 #include "poseidon_goldilocks.hpp"
+#include "polinomial.hpp" // src/starkpil/polinomial.hpp: the element arithmetic FRIProve uses (cubic extension)
 #include <omp.h>
 #include <cstdint>
 
 typedef Goldilocks::Element E;
+
+// link-time glue for what polinomial.hpp declares but this build never calls (src/utils/*.cpp are not compiled)
+zkLog zklog;
+zkLog::zkLog() {}
+void zkLog::log(const zkLogType, const string &, const vector<LogTag> *) {}
+void exitProcess(void) { abort(); }
+bool CompareFeImpl(const Goldilocks::Element &a, const Goldilocks::Element &b) { return Goldilocks::toU64(a) < Goldilocks::toU64(b); }
+bool CompareFeVectorImpl(const std::vector<Goldilocks::Element> &a, const std::vector<Goldilocks::Element> &b) { return a.size() < b.size(); }
 
 extern "C" {
 
@@ -54,5 +63,42 @@ void zkref_merkletree_seq(uint64_t *tree, uint64_t *input, uint64_t ncols, uint6
 // PoseidonGoldilocks::merkletree_batch (poseidon_goldilocks.cpp:302-352)
 void zkref_merkletree_batch(uint64_t *tree, uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t batch, uint64_t dim)
 { PoseidonGoldilocks::merkletree_batch((E *)tree, (E *)input, ncols, nrows, batch, 0, dim); }
+
+// One FRI folding step, si > 0, with the reference's own pieces: the loop body of FRIProve::prove
+// (friProve.cpp:89-106) around NTT_Goldilocks::INTT and Polinomial::{copyElement, mulElement, addElement};
+// polMulAxi (:192-200) and evalPol (:201-217) are members of a class whose translation unit needs the whole prover
+// (transcript, stark_info, json), so their few lines are spelled here over the same Polinomial calls.
+// The per-thread starting value of sinv (:64-81) is shiftInv * wi^g; here it is walked sequentially.
+void zkref_fri_fold(uint64_t *pol2_e_, uint64_t *fri_pol_, uint64_t pol_bits, uint64_t next_bits, uint64_t shift_inv, uint64_t *special_x_)
+{
+    const uint64_t pol2N = 1ull << next_bits, nX = (1ull << pol_bits) / pol2N;
+    Polinomial friPol((E *)fri_pol_, 1ull << pol_bits, FIELD_EXTENSION, FIELD_EXTENSION);
+    Polinomial pol2_e((E *)pol2_e_, pol2N, FIELD_EXTENSION, FIELD_EXTENSION);
+    Polinomial special_x((E *)special_x_, 1, FIELD_EXTENSION, FIELD_EXTENSION);
+    E wi = Goldilocks::inv(Goldilocks::w(pol_bits));
+    E sinv_ = Goldilocks::fromU64(shift_inv);
+    for (uint64_t g = 0; g < pol2N; g++)
+    {
+        Polinomial ppar(nX, FIELD_EXTENSION);
+        Polinomial ppar_c(nX, FIELD_EXTENSION);
+        for (uint64_t i = 0; i < nX; i++) Polinomial::copyElement(ppar, i, friPol, (i * pol2N) + g);
+        NTT_Goldilocks ntt(nX, 1);
+        ntt.INTT(ppar_c.address(), ppar.address(), nX, FIELD_EXTENSION);
+        E r = Goldilocks::one(); // polMulAxi(ppar_c, one, sinv_)
+        for (uint64_t i = 0; i < ppar_c.degree(); i++)
+        {
+            Polinomial::mulElement(ppar_c, i, ppar_c, i, r);
+            r = r * sinv_;
+        }
+        Polinomial::copyElement(pol2_e, g, ppar_c, ppar_c.degree() - 1); // evalPol(pol2_e, g, ppar_c, special_x)
+        for (int64_t i = (int64_t)ppar_c.degree() - 2; i >= 0; i--)
+        {
+            Polinomial aux(1, 3);
+            Polinomial::mulElement(aux, 0, pol2_e, g, special_x, 0);
+            Polinomial::addElement(pol2_e, g, aux, 0, ppar_c, i);
+        }
+        sinv_ = sinv_ * wi;
+    }
+}
 
 } // extern "C"

@@ -143,6 +143,16 @@ def diffs():
     out["cases"].append({"op": "noncanonical", "n": n, "ncols": c, "seed_offset": 3,
                          "rows_override": {"0": "p", "1": "p+1", "2": "2^64-1", "3": "p-1"},
                          "ext_sha256": digest(o), "tree_of_input_sha256": digest(tree)})
+    # one FRI folding step (friProve.cpp:89-106) through the reference's NTT_Goldilocks + Polinomial element ops
+    # (oracle/ref_wrap.cpp zkref_fri_fold); shift_inv and special_x come from the same generator
+    for (pol_bits, next_bits) in [(10, 6), (12, 8), (8, 3), (9, 9), (6, 0), (16, 12)]:
+        a = splitmix_fill((1 << pol_bits) * 3, SEED + 4)
+        aux = splitmix_fill(4, SEED + 5)
+        o = np.zeros((1 << next_bits) * 3, dtype=np.uint64)
+        L.zkref_fri_fold(vp(o), vp(a.copy()), u(pol_bits), u(next_bits), u(int(aux[3])), vp(aux[:3].copy()))
+        L.zkref_canon(vp(o), u(o.size))
+        out["cases"].append({"op": "fri_fold", "pol_bits": pol_bits, "next_bits": next_bits, "seed_offset": 4,
+                             "shift_inv_and_x": "splitmix(seed+5)[3], splitmix(seed+5)[0:3]", "sha256": digest(o), "samples": samples(o)})
     return out
 
 

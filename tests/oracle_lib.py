@@ -80,6 +80,21 @@ class Oracle:
         return self.canon(tree)
 
 
+    def fri_fold(self, fri_pol, pol_bits, next_bits, shift_inv, special_x):
+        """One FRI folding step (friProve.cpp:89-106): fri_pol (2^pol_bits x 3) -> pol2_e (2^next_bits x 3)."""
+        a = np.ascontiguousarray(fri_pol, dtype=np.uint64).reshape(-1)
+        x = np.ascontiguousarray(special_x, dtype=np.uint64)
+        o = np.zeros((1 << next_bits) * 3, dtype=np.uint64)
+        self.L.oracle_fri_fold(_vp(o), _vp(a), u64(pol_bits), u64(next_bits), u64(shift_inv), _vp(x))
+        return self.canon(o).reshape(-1, 3)
+
+    def fri_transpose(self, pol, transpose_bits):
+        a = np.ascontiguousarray(pol, dtype=np.uint64).reshape(-1)
+        o = np.zeros_like(a)
+        self.L.oracle_fri_transpose(_vp(o), _vp(a), u64(a.size // 3), u64(transpose_bits))
+        return o.reshape(-1, 3)
+
+
 class Reference:
     """The compiled unmodified reference (None-like when oracle/_ref/libzkref.so is absent)."""
 
@@ -130,6 +145,13 @@ class Reference:
         else:
             self.L.zkref_merkletree(_vp(tree), _vp(a), u64(ncols), u64(nrows), u64(dim))
         return self.canon(tree)
+
+    def fri_fold(self, fri_pol, pol_bits, next_bits, shift_inv, special_x):
+        a = np.ascontiguousarray(fri_pol, dtype=np.uint64).reshape(-1).copy()
+        x = np.ascontiguousarray(special_x, dtype=np.uint64).copy()
+        o = np.zeros((1 << next_bits) * 3, dtype=np.uint64)
+        self.L.zkref_fri_fold(_vp(o), _vp(a), u64(pol_bits), u64(next_bits), u64(shift_inv), _vp(x))
+        return self.canon(o).reshape(-1, 3)
 
 
 def digest(a):

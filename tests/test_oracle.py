@@ -112,6 +112,13 @@ def test_against_committed_reference_outputs():
             a[0, :] = P; a[1, :] = P + 1; a[2, :] = 2**64 - 1; a[3, :] = P - 1
             assert digest(O.extend_pol(a, 2 * n)) == case["ext_sha256"]
             assert digest(O.merkletree(a, c, n)) == case["tree_of_input_sha256"]
+        elif op == "fri_fold":
+            pb, nb = case["pol_bits"], case["next_bits"]
+            a, aux = _gen((1 << pb) * 3, 4), _gen(4, 5)
+            o = O.fri_fold(a, pb, nb, int(aux[3]), aux[:3])
+            assert digest(o) == case["sha256"], case
+            for i, w in case["samples"].items():
+                assert int(o.reshape(-1)[int(i)]) == int(w, 16)
         else:
             raise AssertionError(op)
 
@@ -135,3 +142,8 @@ def test_against_live_reference():
     for rows, c, dim, batch in [(64, 13, 1, 0), (32, 5, 3, 0), (128, 3, 1, 0), (16, 50, 1, 16), (8, 0, 1, 0)]:
         a = rng.integers(0, 2**63, size=(rows, max(c * dim, 1)), dtype=np.uint64)
         assert (O.merkletree(a, c, rows, dim, batch) == R.merkletree(a, c, rows, dim, batch)).all()
+    for pb, nb in [(4, 2), (8, 4), (10, 5), (5, 5), (7, 0), (12, 8)]:
+        a = rng.integers(0, 2**63, size=((1 << pb), 3), dtype=np.uint64) * np.uint64(2) + np.uint64(1)  # includes words >= p
+        x = rng.integers(0, P, size=3, dtype=np.uint64)
+        sh = int(rng.integers(1, P, dtype=np.uint64))
+        assert (O.fri_fold(a, pb, nb, sh, x) == R.fri_fold(a, pb, nb, sh, x)).all()
