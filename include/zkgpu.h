@@ -116,6 +116,19 @@ int zkgpu_extend_and_merkelize(void *ntt, uint64_t *out_ext, uint64_t *tree, con
  * views directly (merkleTreeGL.hpp:24-32).  const_pols: (1<<n_bits) x n_pols row-major.  Host or device pointers. */
 int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t n_bits, uint64_t n_bits_ext, uint64_t n_pols);
 
+/* ---- FRI layer commit ----
+ * One folding step for si > 0 (src/starkpil/fri/friProve.cpp:44-107): fri_pol holds 2^pol_bits elements of the cubic
+ * extension (3 words each, Polinomial dim 3), pol2_e receives 2^next_bits elements:
+ *   pol2_e[g] = evalPol( polMulAxi( INTT_nX( friPol[i * 2^next_bits + g], i < nX ), 1, shiftInv * w(polBits)^-g ), special_x )
+ * with nX = 2^(pol_bits - next_bits) (polMulAxi :192-200, evalPol :201-217, the per-thread sinv walk :64-81, :105).
+ * shift_inv is polShiftInv of the step (:34-35), special_x the transcript challenge (:30), a host pointer to 3 words.
+ * pol2_e and fri_pol are both host or both device pointers.  (For si == 0 the reference copies friPol, :91-94.) */
+int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits, uint64_t next_bits, uint64_t shift_inv,
+                   const uint64_t *special_x);
+/* FRIProve::getTransposed (friProve.cpp:252-271) on 3-word elements: aux[i*h + j] = pol[j*w + i], w = 2^transpose_bits,
+ * h = degree / w; aux is then the source of MerkleTreeGL(nGroups, groupSize * 3) (:118-122), i.e. of zkgpu_merkletree. */
+int zkgpu_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint64_t transpose_bits);
+
 /* ---- multi-GPU building blocks (device pointers only; one process per GPU, the host side does the exchange) ----
  * LDE of a column shard stored with an arbitrary row stride (columns are independent, ntt_goldilocks.cpp:103-110) */
 int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64_t in_ld, uint64_t n_extended, uint64_t n,

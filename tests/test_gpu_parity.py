@@ -502,3 +502,41 @@ def test_sharded_building_blocks_absorb_copy():
         c0 += w
     zk.sync()
     assert_eq(_host(leaves2), _host(leaves), "absorb without copy")
+
+
+def test_fri_fold_layer_vs_oracle_and_reference_outputs():
+    """one FRI folding step + getTransposed + merkelize of the next layer (friProve.cpp:44-127).
+    Committed outputs of the reference's own NTT_Goldilocks + Polinomial arithmetic (reference_diff.json, op fri_fold),
+    then larger shapes against the oracle, host and device pointers, non-canonical input words."""
+    import torch
+    for case in DIFF["cases"]:
+        if case["op"] != "fri_fold":
+            continue
+        pb, nb = case["pol_bits"], case["next_bits"]
+        a, aux = O.fill((1 << pb) * 3, SEED, 4), O.fill(4, SEED, 5)
+        out = np.zeros((1 << nb) * 3, dtype=np.uint64)
+        zk.FRIProve.fold(out, a, pb, nb, int(aux[3]), aux[:3])
+        assert digest(out) == case["sha256"], case
+    rng = np.random.default_rng(11)
+    for pb, nb in [(14, 10), (18, 14), (20, 15), (12, 12), (9, 0), (13, 5)]:
+        a = rng.integers(0, 2**63, size=(1 << pb) * 3, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+        x = rng.integers(0, 2**63, size=3, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+        sh = int(rng.integers(1, P, dtype=np.uint64))
+        want = O.fri_fold(a, pb, nb, sh, x % np.uint64(P))
+        out = np.zeros((1 << nb) * 3, dtype=np.uint64)
+        zk.FRIProve.fold(out, a, pb, nb, sh, x)
+        assert_eq(out, want, "fri_fold host %d->%d" % (pb, nb))
+        d_a = torch.from_numpy(a.view(np.int64)).cuda()
+        d_o = torch.zeros((1 << nb) * 3, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        zk.FRIProve.fold(d_o, d_a, pb, nb, sh, x)
+        assert_eq(_host(d_o), want, "fri_fold device %d->%d" % (pb, nb))
+        # next layer's tree: transpose into nGroups x (groupSize*3) and merkelize
+        tb = max(nb - 4, 0)
+        auxh = np.zeros_like(out)
+        zk.FRIProve.getTransposed(auxh, out, 1 << nb, tb)
+        assert_eq(auxh, O.fri_transpose(want, tb), "getTransposed")
+        n_groups, group = 1 << tb, (1 << nb) >> tb
+        tree = zk.MerkleTreeGL(n_groups, group * 3, auxh)
+        tree.merkelize()
+        assert_eq(tree.nodes, O.merkletree(auxh, group * 3, n_groups), "FRI layer tree")

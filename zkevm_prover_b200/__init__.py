@@ -17,7 +17,7 @@ import pathlib
 
 import numpy as np
 
-__all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL",
+__all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL", "FRIProve",
            "extend_and_merkelize", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
 
 GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
@@ -62,6 +62,8 @@ ABI_SYMBOLS = {
     "zkgpu_merkle_leaves": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_merkle_absorb": (_int, [_vp, _vp, _u64, _u64, _u64, _int]),
     "zkgpu_merkle_absorb_copy": (_int, [_vp, _vp, _u64, _u64, _u64, _int, _vp, _u64]),
+    "zkgpu_fri_fold": (_int, [_vp, _vp, _u64, _u64, _u64, _vp]),
+    "zkgpu_fri_transpose": (_int, [_vp, _vp, _u64, _u64]),
     "zkgpu_merkle_levels": (_int, [_vp, _u64]),
     "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
 }
@@ -249,6 +251,24 @@ def build_const_tree(image, const_pols, nBits, nBitsExt, nPols):
     """buildConstTree, Goldilocks branch (tools/starkpil/bctree/build_const_tree.cpp:533-596): fills `image` with
     [nPols, nExt, extended constant polynomials, tree nodes]."""
     _check(lib().zkgpu_build_const_tree(_ptr(image), _ptr(const_pols), nBits, nBitsExt, nPols))
+
+
+class FRIProve:
+    """The data-parallel pieces of FRIProve::prove (src/starkpil/fri/friProve.cpp); the transcript and the proof
+    object stay with the caller."""
+
+    @staticmethod
+    def fold(pol2_e, friPol, polBits, nextBits, shiftInv, special_x):
+        """Folding step si > 0 (friProve.cpp:44-107): friPol (2^polBits x 3) -> pol2_e (2^nextBits x 3)."""
+        x = np.ascontiguousarray(special_x, dtype=np.uint64)
+        if x.size != 3:
+            raise ValueError("special_x is one cubic-extension element (3 words)")
+        _check(lib().zkgpu_fri_fold(_ptr(pol2_e), _ptr(friPol), polBits, nextBits, int(shiftInv), _ptr(x)))
+
+    @staticmethod
+    def getTransposed(aux, pol, degree, trasposeBits):
+        """friProve.cpp:252-271 on 3-word elements."""
+        _check(lib().zkgpu_fri_transpose(_ptr(aux), _ptr(pol), degree, trasposeBits))
 
 
 def extend_and_merkelize(ntt, out_ext, tree, inp, N_Extended, N, ncols):

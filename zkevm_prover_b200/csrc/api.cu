@@ -442,6 +442,63 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// FRI folding step (src/starkpil/fri/friProve.cpp:26-107, 192-217, 252-271).  Elements of the cubic extension
+// F_p[x]/(x^3 - x - 1) are 3 consecutive words (Polinomial with dim 3).
+// ---------------------------------------------------------------------------------------------------
+// Polinomial::mulElement dim 3 x dim 3 (polinomial.hpp:193-206); a, b canonical, result canonical
+__device__ __forceinline__ void gl3_mul(u64 (&o)[3], const u64 (&a)[3], const u64 (&b)[3])
+{
+    const u64 A = gl::mul(gl::add(a[0], a[1]), gl::add(b[0], b[1]));
+    const u64 B = gl::mul(gl::add(a[0], a[2]), gl::add(b[0], b[2]));
+    const u64 C = gl::mul(gl::add(a[1], a[2]), gl::add(b[1], b[2]));
+    const u64 D = gl::mul(a[0], b[0]), E = gl::mul(a[1], b[1]), F = gl::mul(a[2], b[2]);
+    const u64 G = gl::canon(gl::sub(D, E));
+    o[0] = gl::canon(gl::sub(gl::add(C, G), F));
+    o[1] = gl::canon(gl::sub(gl::sub(gl::sub(gl::add(A, C), E), E), D));
+    o[2] = gl::canon(gl::sub(B, G));
+}
+// coef: the size-nX INTT of every group, [nX][pol2N][3] (group g = columns 3g..3g+2 of the nX x 3 pol2N matrix view
+// of friPol).  polMulAxi scales coefficient i by sinv_g^i and evalPol evaluates at special_x: together the Horner
+// evaluation at y_g = special_x * sinv_g, sinv_g = shiftInv * w(polBits)^-g.  One thread per group; reads are
+// coalesced across g.
+__global__ void __launch_bounds__(256) fri_fold_kernel(u64 *out, const u64 *coef, u64 nx, u64 pol2n, u64 shift_inv, u64 wi, u64 x0, u64 x1,
+                                                        u64 x2)
+{
+    const u64 g = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= pol2n) return;
+    u64 s = shift_inv, b = wi;
+    for (u64 e = g; e; e >>= 1)
+    {
+        if (e & 1) s = gl::mul(s, b);
+        b = gl::mul(b, b);
+    }
+    const u64 y[3] = {gl::mul(x0, s), gl::mul(x1, s), gl::mul(x2, s)};
+    const u64 *c = coef + g * 3;
+    const u64 stride = pol2n * 3;
+    u64 res[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) res[k] = gl::canon(c[(nx - 1) * stride + k]);
+    for (u64 i = nx - 1; i-- > 0;)
+    {
+        u64 t[3];
+        gl3_mul(t, res, y);
+#pragma unroll
+        for (int k = 0; k < 3; k++) res[k] = gl::canon(gl::add(t[k], gl::canon(c[i * stride + k])));
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) out[g * 3 + k] = res[k];
+}
+static inline unsigned nblocks(u64 n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+// getTransposed: aux[i*h + j] = pol[j*w + i] (3-word elements); one thread per destination word
+__global__ void __launch_bounds__(256) fri_transpose_kernel(u64 *aux, const u64 *pol, u64 w, u64 h)
+{
+    const u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= w * h * 3) return;
+    const u64 e = t / 3, k = t - e * 3, i = e / h, j = e - i * h;
+    aux[t] = pol[(j * w + i) * 3 + k];
+}
+
 } // namespace zk
 
 using namespace zk;
@@ -1123,6 +1180,104 @@ int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t
     ZK_CUDA(cudaMemcpyAsync(image, header, sizeof(header), cudaMemcpyDefault, g_ctx.cur));
     ZK_CUDA(cudaStreamSynchronize(g_ctx.cur)); // header[] is a stack buffer
     return zkgpu_extend_and_merkelize(nullptr, image + 2, image + 2 + n_pols * n_ext, const_pols, n_ext, n, n_pols);
+}
+
+int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits, uint64_t next_bits, uint64_t shift_inv,
+                   const uint64_t *special_x)
+{
+    LOCK;
+    if (!pol2_e || !fri_pol || !special_x)
+    {
+        set_error("fri_fold: NULL argument");
+        return -1;
+    }
+    if (next_bits > pol_bits || pol_bits > 32)
+    {
+        set_error("fri_fold: need next_bits <= pol_bits <= 32 (got %llu, %llu)", (unsigned long long)next_bits, (unsigned long long)pol_bits);
+        return -1;
+    }
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const u64 pol2n = (u64)1 << next_bits, nx = (u64)1 << (pol_bits - next_bits), words_in = ((u64)3 << pol_bits), words_out = pol2n * 3;
+    const bool dev = is_device_ptr(fri_pol);
+    if (dev != is_device_ptr(pol2_e))
+    {
+        set_error("fri_fold: pol2_e and fri_pol must both be host or both be device pointers");
+        return -1;
+    }
+    Staged in, coef, out;
+    const u64 *d_in = fri_pol;
+    u64 *d_out = pol2_e;
+    ZK_TRY(coef.alloc(words_in));
+    if (!dev)
+    {
+        ZK_TRY(in.alloc(words_in));
+        ZK_TRY(out.alloc(words_out));
+        ZK_CUDA(cudaMemcpyAsync(in.d, fri_pol, words_in * sizeof(u64), cudaMemcpyHostToDevice, st));
+        d_in = in.d;
+        d_out = out.d;
+    }
+    // every group's INTT at once: ppar[i] = friPol[i*pol2N + g] is row i, columns 3g..3g+2 of an nX x 3 pol2N matrix
+    const unsigned L = ilog2(nx);
+    Scale pre, post;
+    if (nx > 1)
+    {
+        post.mode = SCALE_CONST;
+        post.konst = gl::pow_slow(nx % GL_P, GL_P - 2);
+    }
+    if (L > 8) ZK_TRY(ensure_scratch(words_in));
+    ZK_TRY(ntt_transform(coef.d, words_out, d_in, words_out, g_ctx.scratch, L, words_out, true, pre, post, st));
+    const u64 wi = gl::pow_slow(gl::root_of_unity((unsigned)pol_bits), GL_P - 2); // Goldilocks::inv(Goldilocks::w(polBits)), friProve.cpp:36
+    fri_fold_kernel<<<nblocks(pol2n, 256), 256, 0, st>>>(d_out, coef.d, nx, pol2n, shift_inv % GL_P, wi, special_x[0] % GL_P,
+                                                         special_x[1] % GL_P, special_x[2] % GL_P);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    if (!dev) ZK_CUDA(cudaMemcpyAsync(pol2_e, d_out, words_out * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st)); // the staging buffers are freed on return
+    return 0;
+}
+
+int zkgpu_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint64_t transpose_bits)
+{
+    LOCK;
+    if (degree == 0) return 0;
+    if (!aux || !pol || aux == pol)
+    {
+        set_error("fri_transpose: NULL or aliased arguments");
+        return -1;
+    }
+    const u64 w = (u64)1 << transpose_bits;
+    if (transpose_bits > 32 || degree % w)
+    {
+        set_error("fri_transpose: degree %llu is not a multiple of 2^%llu", (unsigned long long)degree, (unsigned long long)transpose_bits);
+        return -1;
+    }
+    NEED_CTX;
+    cudaStream_t st = g_ctx.cur;
+    const u64 h = degree / w, words = degree * 3;
+    const bool dev = is_device_ptr(pol);
+    if (dev != is_device_ptr(aux))
+    {
+        set_error("fri_transpose: aux and pol must both be host or both be device pointers");
+        return -1;
+    }
+    if (dev)
+    {
+        fri_transpose_kernel<<<nblocks(words, 256), 256, 0, st>>>(aux, pol, w, h);
+        ZK_LAUNCHED();
+        ZK_CUDA(cudaGetLastError());
+        return 0;
+    }
+    Staged in, out;
+    ZK_TRY(in.alloc(words));
+    ZK_TRY(out.alloc(words));
+    ZK_CUDA(cudaMemcpyAsync(in.d, pol, words * sizeof(u64), cudaMemcpyHostToDevice, st));
+    fri_transpose_kernel<<<nblocks(words, 256), 256, 0, st>>>(out.d, in.d, w, h);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    ZK_CUDA(cudaMemcpyAsync(aux, out.d, words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st));
+    return 0;
 }
 
 } // extern "C"
