@@ -359,14 +359,28 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
     pipe_event(nullptr, st);
     g_ctx.segs.clear();
     // strip boundaries: full-width strips of w columns, except that with a host-resident trace the first two strips are
-    // narrow (32, then 64 columns) so that little of the first host->device copy is exposed before compute starts
+    // narrow (32, then 64 columns) so that little of the first host->device copy is exposed before compute starts.
+    // Measured on one box (profiles/r1_strip_ramp_ab.txt, e2e ms at H): 32,64 -> 1440; 16,32,64 -> 1439; 32,48,80 -> 1441;
+    // 16,48 -> 1468; no ramp -> 1491; 16,32,48,80 -> 1544 (more strips cost more than the exposed copy they save).
     std::vector<u64> start;
     for (u64 c = 0; c < ncols;)
     {
         start.push_back(c);
         u64 cw = w;
-        if (!in_dev && start.size() == 1 && w > 32) cw = 32;
-        if (!in_dev && start.size() == 2 && w > 64) cw = 64;
+        // ZKGPU_STRIP_RAMP="a,b,c,d" overrides the ramp (development knob, multiples of 16)
+        static u64 ramp[4] = {32, 64, ~0ull, ~0ull};
+        static bool ramp_init = false;
+        if (!ramp_init)
+        {
+            ramp_init = true;
+            if (const char *e = getenv("ZKGPU_STRIP_RAMP"))
+            {
+                unsigned long long v[4] = {0, 0, 0, 0};
+                const int k = sscanf(e, "%llu,%llu,%llu,%llu", &v[0], &v[1], &v[2], &v[3]);
+                for (int i = 0; i < 4; i++) ramp[i] = (i < k && v[i] >= 16) ? (v[i] & ~15ull) : ~0ull;
+            }
+        }
+        if (!in_dev && start.size() <= 4 && w > ramp[start.size() - 1]) cw = ramp[start.size() - 1];
         c += cw;
     }
     start.push_back(ncols);
@@ -1101,6 +1115,7 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
         return -1;
     }
     const u64 tree_words = (2 * n_ext - 1) * 4;
+    u64 leaves_sent = 0;
     Staged dtree;
     u64 *d_tree = tree;
     if (!tree_dev)
@@ -1139,11 +1154,23 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     {
         ZK_TRY(commit_pipeline(out_ext, out_dev, d_tree, input, in_dev, log_n, log_b, ncols, st));
         ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+        if (!tree_dev)
+        {
+            // the leaf level (half of the tree) goes back to the host while the node levels are hashed
+            ZK_CUDA(cudaStreamWaitEvent(g_ctx.d2h, g_ctx.ev[2], 0));
+            ZK_CUDA(cudaMemcpyAsync(tree, d_tree, n_ext * 4 * sizeof(u64), cudaMemcpyDeviceToHost, g_ctx.d2h));
+            ZK_CUDA(cudaEventRecord(g_ctx.out_free[0], g_ctx.d2h));
+            leaves_sent = n_ext * 4;
+        }
         ZK_TRY(merkle_levels(d_tree, n_ext, st));
         ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
     }
     g_ctx.timed = true;
-    if (!tree_dev) ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    if (!tree_dev)
+    {
+        ZK_CUDA(cudaMemcpyAsync(tree + leaves_sent, d_tree + leaves_sent, (tree_words - leaves_sent) * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        if (leaves_sent) ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[0], 0));
+    }
     ZK_CUDA(cudaEventRecord(g_ctx.ev[5], st));
     if (!in_dev || !out_dev || !tree_dev)
     {
