@@ -358,17 +358,17 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
 
     pipe_event(nullptr, st);
     g_ctx.segs.clear();
-    // strip boundaries: full-width strips of w columns, except that with a host-resident trace the first two strips are
-    // narrow (32, then 64 columns) so that little of the first host->device copy is exposed before compute starts.
-    // Measured on one box (profiles/r1_strip_ramp_ab.txt, e2e ms at H): 32,64 -> 1440; 16,32,64 -> 1439; 32,48,80 -> 1441;
-    // 16,48 -> 1468; no ramp -> 1491; 16,32,48,80 -> 1544 (more strips cost more than the exposed copy they save).
+    // strip boundaries: full-width strips of w columns, except that with a host-resident trace the first strips ramp up
+    // (16, 32, 48, 64 columns): only the copy of the first 16 columns is exposed and each later copy (1.33 ms per column)
+    // nearly fits under the compute of the strip before it (2.0 ms per column).  Timelines (ZKGPU_PIPE_TRACE=1,
+    // profiles/r1_e2e_pipeline_trace.txt) at H: 32,64 -> 1438 ms; 16,32,48,80 -> 1435 ms; 16,32,48,64 -> 1420 ms.
     std::vector<u64> start;
     for (u64 c = 0; c < ncols;)
     {
         start.push_back(c);
         u64 cw = w;
         // ZKGPU_STRIP_RAMP="a,b,c,d" overrides the ramp (development knob, multiples of 16)
-        static u64 ramp[4] = {32, 64, ~0ull, ~0ull};
+        static u64 ramp[4] = {16, 32, 48, 64};
         static bool ramp_init = false;
         if (!ramp_init)
         {
@@ -386,12 +386,21 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
     start.push_back(ncols);
     const u64 nstrips = start.size() - 1;
     auto strip_cols = [&](u64 s) { return start[s + 1] - start[s]; };
+    // ZKGPU_PIPE_TRACE=1: print the timeline of the copies and kernels of this call (development aid; synchronises)
+    static const bool trace = getenv("ZKGPU_PIPE_TRACE") != nullptr;
+    std::vector<std::pair<int, int>> h2d_ev;
+    int t_origin = -1;
+    if (trace) ZK_TRY(pipe_event(&t_origin, st));
     auto issue_h2d = [&](u64 s) -> int {
         const int b = (int)(s & 1);
         const u64 cw = strip_cols(s);
         if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[b], 0));
+        int t0 = -1, t1 = -1;
+        if (trace) ZK_TRY(pipe_event(&t0, g_ctx.h2d));
         ZK_CUDA(cudaMemcpy2DAsync(in_buf[b], cw * sizeof(u64), input + start[s], ncols * sizeof(u64), cw * sizeof(u64), n,
                                   cudaMemcpyHostToDevice, g_ctx.h2d));
+        if (trace) ZK_TRY(pipe_event(&t1, g_ctx.h2d));
+        if (trace) h2d_ev.push_back({t0, t1});
         ZK_CUDA(cudaEventRecord(g_ctx.in_ready[b], g_ctx.h2d));
         return 0;
     };
@@ -452,6 +461,25 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
         // the caller-visible completion point is the compute stream: make it wait for the last device->host strips
         ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[0], 0));
         ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[1], 0));
+    }
+    if (trace)
+    {
+        ZK_CUDA(cudaStreamSynchronize(st));
+        if (g_ctx.h2d) ZK_CUDA(cudaStreamSynchronize(g_ctx.h2d));
+        auto at = [&](int e) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, g_ctx.pool[t_origin], g_ctx.pool[e]);
+            return ms;
+        };
+        fprintf(stderr, "[zkgpu pipe] strip cols | h2d begin..end | lde begin..end | absorb end   (ms from call start)\n");
+        for (u64 s = 0; s < nstrips; s++)
+        {
+            const auto &l = g_ctx.segs[2 * s], &a = g_ctx.segs[2 * s + 1];
+            float hb = -1, he = -1;
+            if (s < h2d_ev.size()) hb = at(h2d_ev[s].first), he = at(h2d_ev[s].second);
+            fprintf(stderr, "[zkgpu pipe] %2llu %4llu | %8.1f %8.1f | %8.1f %8.1f | %8.1f\n", (unsigned long long)s,
+                    (unsigned long long)strip_cols(s), hb, he, at(l.a), at(l.b), at(a.b));
+        }
     }
     return 0;
 }
