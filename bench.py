@@ -247,7 +247,7 @@ def run_ours(args):
                 e = torch.cuda.Event(enable_timing=True)
                 e.record(stream)
                 ev.append((name, e))
-            rows, tree = dc.commit_sharded_pipelined(ops, dist, inputs or pieces, n, n_ext, c, rounds, timers=mark if timed else None)
+            rows, tree = dc.commit_sharded_pipelined(ops, dist, inputs or pieces, n, n_ext, c, None, timers=mark if timed else None)
             keep["rows"], keep["tree"] = rows, tree
             if timed:
                 torch.cuda.synchronize()

@@ -115,7 +115,8 @@ def _worker_pipe(rank, world, port, n, b, c, rounds, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,n,b,c,rounds", [(2, 64, 2, 45, 2), (4, 32, 2, 100, 3), (2, 32, 2, 21, None), (4, 16, 4, 9, None)])
+@pytest.mark.parametrize("world,n,b,c,rounds", [(2, 64, 2, 45, 2), (4, 32, 2, 100, 3), (2, 32, 2, 21, None), (4, 16, 4, 9, None),
+                                                  (2, 32, 2, 203, None)])  # 203 columns on 2 ranks: ramped rounds 16, 32, then the rest
 def test_commit_sharded_pipelined_gloo(world, n, b, c, rounds):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -133,12 +134,20 @@ def test_commit_sharded_pipelined_gloo(world, n, b, c, rounds):
 
 def test_piece_plan():
     K, plan = dc.piece_plan(665, 8)
-    assert K == 3 and plan[0][0] == (0, 32) and plan[2][7] == (648, 17)
+    assert K == 3 and plan[0][0] == (0, 16) and plan[1][0] == (128, 32) and plan[2][7] == (640, 25)
+    assert dc.piece_plan(665, 8, 3)[1][0][0] == (0, 32)  # explicit rounds: equal rounds
     flat = [p for r in plan for p in r]
     assert all(a[0] + a[1] == b[0] for a, b in zip(flat[:-1], flat[1:])) and flat[-1][0] + flat[-1][1] == 665
     assert all(w % 8 == 0 for _, w in flat[:-1])
     per_rank = [sum(plan[k][g][1] for k in range(K)) for g in range(8)]
     assert max(per_rank) - min(per_rank) <= 16
+    for world in (1, 2, 4):
+        K, plan = dc.piece_plan(665, world)
+        flat = [p for r in plan for p in r]
+        assert all(a[0] + a[1] == b[0] for a, b in zip(flat[:-1], flat[1:])) and flat[-1][0] + flat[-1][1] == 665
+        assert all(w % 8 == 0 for _, w in flat[:-1]) and plan[0][0][1] == 16 and max(w for _, w in flat) <= 64
+        per_rank = [sum(plan[k][g][1] for k in range(K)) for g in range(world)]
+        assert max(per_rank) - min(per_rank) <= 8
     assert dc.piece_plan(9, 4) == (1, [[(0, 8), (8, 1), (9, 0), (9, 0)]])
 
 

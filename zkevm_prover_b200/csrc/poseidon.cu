@@ -4,14 +4,16 @@
 // (reference src/goldilocks/src/poseidon_goldilocks.cpp:166-228, 229-265, 266-301, 302-352; scalar statement of
 // the same math :5-112) and the AVX2 field helpers they use (goldilocks_base_field_avx.hpp:176-573).
 //
-// One thread owns one 12-word state in registers.  The round structure is the reference's "optimised"
-// Poseidon (4 full + 22 sparse partial + 4 full rounds, x^7), evaluated with GPU-shaped arithmetic:
-//   * S-box: 4 un-normalised multiplies (gl::mul_nc), operands may be any 64-bit word;
-//   * full-round MDS (entries <= 41): the state is split in 32-bit halves, each output is two 64-bit
-//     IMAD.WIDE accumulators (sum of M*lo, sum of M*hi) recombined and folded once (2^64 = 2^32-1);
-//   * dense P matrix and sparse-round dot products: 128-bit products accumulated in a 160-bit carry chain,
-//     folded once per output;
-//   * sparse-round column update st[i] += s0*S[i]: product and addend folded together.
+// One thread owns one 12-word state in registers.  The permutation (4 full + 22 partial + 4 full rounds, x^7) is
+// evaluated in its DENSE form — every round is "S-box layer, add constants, multiply by the MDS matrix" — which is
+// algebraically the reference's "optimised" sparse form (same outputs word for word) but maps to the SM differently:
+//   * S-box: 4 un-normalised 64-bit modular multiplies (gl::mul_nc) on the integer-multiply pipe;
+//   * MDS (entries <= 41): the state is split in 32-bit halves, converted to doubles, and the circulant product is done
+//     EXACTLY on the FP64 pipe through a size-4 DFT over the Gaussian integers (78 DADD/DFMA per half-vector); one
+//     fold per output brings the 74-bit result back to a 64-bit word;
+//   * partial rounds go in pairs with the eleven passive words kept in the FP / DFT domain between the two products.
+// The sparse form on the integer pipes only (ZK_POS_FP64=0: IMAD.WIDE MDS, 160-bit accumulators for the dense P and
+// the sparse rows) is kept for comparison (tools/pos_bench.cu): 849 against 1438 Mperm/s.
 // Constants live in __constant__ memory (every thread of a warp reads the same word: broadcast).
 #include "gl64.cuh"
 #include "zk_internal.h"

@@ -135,19 +135,36 @@ def exchange_async(dist, send, recv, send_splits, recv_splits, group=None):
 def piece_plan(ncols, world, rounds=None):
     """Column ownership of the pipelined commit: the row is cut into rounds x world consecutive pieces, piece (k, g)
     belonging to rank g in round k, every piece a whole number of 8-column sponge blocks (the last one holds the ragged
-    tail).  Returns (rounds, plan) with plan[k][g] = (first column, width).  665 columns on 8 ranks: 3 rounds of
-    pieces 32,32,...,24 columns."""
+    tail).  Returns (rounds, plan) with plan[k][g] = (first column, width).
+
+    With rounds=None the rounds ramp up: 2 blocks per rank, then 4, then the rest in equal rounds of at most 8 blocks
+    per rank — with a host-resident trace only the copy of the first (small) piece is exposed and each later copy fits
+    under the compute of the round before it (same reasoning as the single-GPU strip ramp, csrc/api.cu).
+    665 columns on 8 ranks: 3 rounds of 16-, 32- and 40/32-column pieces.  An explicit `rounds` gives equal rounds."""
     blocks = -(-ncols // 8)
-    if rounds is None:
-        rounds = max(1, min(6, blocks // (3 * world)))
-    pieces = rounds * world
-    base, extra = divmod(blocks, pieces)
-    flat, c0 = [], 0
-    for i in range(pieces):
-        w = min((base + (1 if i < extra else 0)) * 8, ncols - c0)
-        flat.append((c0, w))
-        c0 += w
-    return rounds, [flat[k * world:(k + 1) * world] for k in range(rounds)]
+    if rounds is not None:
+        per_round = [blocks // rounds + (1 if k < blocks % rounds else 0) for k in range(rounds)]
+    else:
+        per_round, left = [], blocks
+        for want in (2 * world, 4 * world):
+            if left >= want + 4 * world:
+                per_round.append(want)
+                left -= want
+        k = max(1, -(-left // (8 * world)))
+        per_round += [left // k + (1 if i < left % k else 0) for i in range(k)]
+        rounds = len(per_round)
+    plan, c0, rot = [], 0, 0
+    for nb in per_round:
+        base, extra = divmod(nb, world)
+        row = []
+        for g in range(world):
+            # the odd blocks of a round go to a different group of ranks each round, so that column counts stay level
+            w = min((base + (1 if (g - rot) % world < extra else 0)) * 8, ncols - c0)
+            row.append((c0, w))
+            c0 += w
+        plan.append(row)
+        rot = (rot + extra) % world
+    return rounds, plan
 
 
 def commit_sharded_pipelined(ops, dist, pieces_in, n, n_ext, ncols, rounds=None, group=None, timers=None):
