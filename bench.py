@@ -342,6 +342,21 @@ def run_ours(args):
                 "note": "arithmetic-bound kernel (about 1.4e9 Poseidon permutations per step: 472 64-bit modular multiplies on the "
                         "integer-multiply pipe + 30 MDS products on the FP64 pipe each; the two pipes share a dispatch port that ncu "
                         "shows 95 % busy: profiles/r1_ncu_quick_poseidon_fp64.txt); HBM fraction is low by nature"}
+    # arithmetic roof of the sponge kernel: the integer-multiply and FP64 pipes share one dispatch port per SM sub-partition
+    # (profiles/r1_int_bench_fp64.txt: IMAD.WIDE/IMAD.HI occupy it 4 clocks per warp instruction, DFMA/DADD 2).  One
+    # permutation needs at least 472 products x (4 IMAD.WIDE + 1 IMAD.HI) and 8 x 156 + 11 x 256 FP64 operations on it
+    #  = 17568 clocks per warp of 32 permutations; the peak below is that bound at the measured SM clock.
+    port_clocks = 472 * 5 * 4 + (8 * 156 + 11 * 256) * 2
+    if roofline["permutations_per_s"]:
+        sm_clock = 1.965e9
+        try:
+            sm_clock = float(clocks["sm_mhz"]) * 1e6 if clocks and clocks.get("sm_mhz") else sm_clock
+        except Exception:
+            pass
+        peak_perm = 148 * 4 * sm_clock / port_clocks * 32
+        roofline["arithmetic"] = {"bound": "IMAD+FP64 dispatch port", "achieved": roofline["permutations_per_s"], "peak": peak_perm,
+                                  "unit": "permutations/s per GPU", "frac": roofline["permutations_per_s"] / peak_perm,
+                                  "port_clocks_per_warp_permutation": port_clocks}
     lde_ms = stages.get("lde")
     lde_bytes = 8 * c * (n + n_ext) / world
     roofline_lde = {"stage": "extendPol (INTT + coset NTTs, all passes)", "bound": "hbm",
