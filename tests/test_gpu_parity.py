@@ -530,6 +530,7 @@ def test_fri_fold_layer_vs_oracle_and_reference_outputs():
         d_o = torch.zeros((1 << nb) * 3, dtype=torch.int64, device="cuda")
         torch.cuda.synchronize()
         zk.FRIProve.fold(d_o, d_a, pb, nb, sh, x)
+        zk.sync()  # device pointers: the call returns after enqueueing on the library's stream
         assert_eq(_host(d_o), want, "fri_fold device %d->%d" % (pb, nb))
         # next layer's tree: transpose into nGroups x (groupSize*3) and merkelize
         tb = max(nb - 4, 0)

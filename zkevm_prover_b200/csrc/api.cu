@@ -1260,10 +1260,14 @@ int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits,
         set_error("fri_fold: pol2_e and fri_pol must both be host or both be device pointers");
         return -1;
     }
-    Staged in, coef, out;
+    Staged in, out;
     const u64 *d_in = fri_pol;
     u64 *d_out = pol2_e;
-    ZK_TRY(coef.alloc(words_in));
+    // every group's INTT at once: ppar[i] = friPol[i*pol2N + g] is row i, columns 3g..3g+2 of an nX x 3 pol2N matrix.
+    // The coefficients live in the library's scratch area (followed by the transform's own scratch for nX > 256).
+    const unsigned L = ilog2(nx);
+    ZK_TRY(ensure_scratch(words_in * (L > 8 ? 2 : 1)));
+    u64 *coef = g_ctx.scratch;
     if (!dev)
     {
         ZK_TRY(in.alloc(words_in));
@@ -1272,24 +1276,24 @@ int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits,
         d_in = in.d;
         d_out = out.d;
     }
-    // every group's INTT at once: ppar[i] = friPol[i*pol2N + g] is row i, columns 3g..3g+2 of an nX x 3 pol2N matrix
-    const unsigned L = ilog2(nx);
     Scale pre, post;
     if (nx > 1)
     {
         post.mode = SCALE_CONST;
         post.konst = gl::pow_slow(nx % GL_P, GL_P - 2);
     }
-    if (L > 8) ZK_TRY(ensure_scratch(words_in));
-    ZK_TRY(ntt_transform(coef.d, words_out, d_in, words_out, g_ctx.scratch, L, words_out, true, pre, post, st));
+    ZK_TRY(ntt_transform(coef, words_out, d_in, words_out, g_ctx.scratch + words_in, L, words_out, true, pre, post, st));
     const u64 wi = gl::pow_slow(gl::root_of_unity((unsigned)pol_bits), GL_P - 2); // Goldilocks::inv(Goldilocks::w(polBits)), friProve.cpp:36
-    fri_fold_kernel<<<nblocks(pol2n, 256), 256, 0, st>>>(d_out, coef.d, nx, pol2n, shift_inv % GL_P, wi, special_x[0] % GL_P,
+    fri_fold_kernel<<<nblocks(pol2n, 256), 256, 0, st>>>(d_out, coef, nx, pol2n, shift_inv % GL_P, wi, special_x[0] % GL_P,
                                                          special_x[1] % GL_P, special_x[2] % GL_P);
     ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
-    if (!dev) ZK_CUDA(cudaMemcpyAsync(pol2_e, d_out, words_out * sizeof(u64), cudaMemcpyDeviceToHost, st));
-    ZK_CUDA(cudaStreamSynchronize(st)); // the staging buffers are freed on return
-    return 0;
+    if (!dev)
+    {
+        ZK_CUDA(cudaMemcpyAsync(pol2_e, d_out, words_out * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        ZK_CUDA(cudaStreamSynchronize(st)); // the staging buffers are freed on return
+    }
+    return 0; // device pointers: enqueued, like the other entry points
 }
 
 int zkgpu_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint64_t transpose_bits)
