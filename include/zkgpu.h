@@ -28,7 +28,8 @@ extern "C" {
 #endif
 
 /* ---- runtime ---- */
-int zkgpu_init(int device);            /* select the device (-1 = keep the current one) and create the context */
+int zkgpu_init(int device);            /* bind the calling host thread to this device's context (created on first use);
+                                          -1 = the context the thread already has, else the process default */
 int zkgpu_set_stream(void *cuda_stream); /* cudaStream_t to enqueue on (0 = the legacy default stream);
                                             (void*)-1 = back to the library's own non-blocking stream */
 int zkgpu_sync(void);                  /* wait for everything enqueued on the library stream */
@@ -149,6 +150,36 @@ int zkgpu_merkle_levels(uint64_t *tree, uint64_t num_rows);
 /* gather/scatter between a row-major matrix and a packed block: dst[r*ncols + c] = src[(row0 + r)*src_ld + col0 + c]
  * (pack) or the inverse (unpack) — used around the column-shard -> row-shard all-to-all */
 int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64_t src_ld, uint64_t nrows, uint64_t ncols);
+
+/* ---- the commit stage over all GPUs of one box ----
+ * The reference prover is one process with one proof in flight (src/prover/prover.cpp:182-221) whose commit stages are plain
+ * method calls (src/starkpil/starks.cpp:51-58); so the multi-GPU commit has two forms behind this ABI:
+ *
+ * (1) single process (what the drop-in classes use): zkgpu_init_multi(ngpu) creates one context per device 0..ngpu-1,
+ *     enables peer access and an NCCL communicator over them.  From then on zkgpu_extend_and_merkelize with a HOST trace is
+ *     committed by all GPUs (one worker thread per device): out_ext may be a host buffer (every GPU copies its rows home) or
+ *     NULL (the extended trace stays on the devices as row shards); tree may be a host buffer or memory of device 0.
+ *     ngpu <= 0: all visible devices.  ngpu must be a power of two.
+ * (2) one process per GPU (torchrun-style launchers): rank 0 calls zkgpu_nccl_unique_id and hands the 128 bytes to the other
+ *     ranks by any means; every rank calls zkgpu_init(local_device) and zkgpu_dist_init(id, rank, world), then
+ *     zkgpu_dist_commit with ITS column pieces of the trace.  zkgpu_dist_plan tells which columns those are:
+ *     c0[k*world + g], w[k*world + g] = first column and width of the piece of rank g in round k (rounds <= 16).
+ *     pieces[k] is an N x w matrix with row stride piece_ld[k]; all device pointers (host_input = 0) or all host pointers
+ *     (host_input = 1: staged round by round under the compute; the plan differs, ask zkgpu_dist_plan with the same flag).
+ *     gather_tree != 0 (same value on every rank): rank 0's `tree` (device or host, (2*NExt-1)*4 words) receives the whole
+ *     level-major node array; other ranks pass NULL.  gather_tree == 0: the tree stays sharded.
+ *     After the call zkgpu_dist_rows gives this rank's row shard of the extended trace (rows [rank*R, (rank+1)*R), R = NExt /
+ *     world, row-major with ncols columns: the layout MerkleTreeGL::source has) and its subtree ((2R-1)*4 words).
+ * The column-shard -> row-shard exchange is done by the LDE's own stores into the peers' row shards over NVLink (peer
+ * access / CUDA IPC); without peer access, or with ZKGPU_EXCHANGE=nccl, by grouped ncclSend/ncclRecv per round. */
+int zkgpu_init_multi(int ngpu);
+int zkgpu_nccl_unique_id(void *out128);
+int zkgpu_dist_init(const void *nccl_unique_id, int rank, int world);
+int zkgpu_dist_info(int *rank, int *world, int *peer_stores);
+int zkgpu_dist_plan(uint64_t ncols, int world, int host_input, int *rounds, uint64_t *c0, uint64_t *w);
+int zkgpu_dist_commit(void *ntt, uint64_t *tree, const uint64_t *const *pieces, const uint64_t *piece_ld, int host_input, int gather_tree,
+                      uint64_t n_extended, uint64_t n, uint64_t ncols);
+int zkgpu_dist_rows(uint64_t **rows, uint64_t *num_rows, uint64_t *num_cols, uint64_t **subtree);
 
 #ifdef __cplusplus
 }

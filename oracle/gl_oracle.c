@@ -321,6 +321,28 @@ void oracle_fill(u64 *x, u64 n, u64 seed, u64 offset)
     for (u64 i = 0; i < n; i++) x[i] = splitmix64(seed + offset + i) % GL_P;
 }
 
+
+/* column block [c0, c0+w) of the row-major synthetic trace of ncols columns: dst[i*w + j] = gen(i*ncols + c0 + j) */
+void oracle_fill_block(u64 *dst, u64 nrows, u64 c0, u64 w, u64 ncols, u64 seed)
+{
+#pragma omp parallel for
+    for (u64 i = 0; i < nrows; i++)
+        for (u64 j = 0; j < w; j++) dst[i * w + j] = splitmix64(seed + i * ncols + c0 + j) % GL_P;
+}
+
+/* The matrix of the reference's Merkle known-answer tests (tests.cpp:1887-1900, benchs/bench.cpp:409-424): rows 0 and 1
+ * are 1..ncols, row j = row j-2 + row j-1.  Canonical words (the reference's are Goldilocks::add results, equal mod p). */
+void oracle_merkle_kat_matrix(u64 *m, u64 nrows, u64 ncols)
+{
+    for (u64 i = 0; i < ncols; i++)
+    {
+        m[i] = i + 1;
+        if (nrows > 1) m[ncols + i] = i + 1;
+    }
+    for (u64 j = 2; j < nrows; j++)
+        for (u64 i = 0; i < ncols; i++) m[j * ncols + i] = gl_canon(gl_add(m[(j - 2) * ncols + i], m[(j - 1) * ncols + i]));
+}
+
 /* ---------------- FRI folding step (src/starkpil/fri/friProve.cpp:26-107) ----------------
  * Elements of the cubic extension F_p[x]/(x^3 - x - 1) are 3 consecutive words.
  * Polinomial::mulElement, dim 3 x dim 3 (src/starkpil/polinomial.hpp:193-206). */

@@ -23,6 +23,69 @@ bool CompareFeVectorImpl(const std::vector<Goldilocks::Element> &a, const std::v
 extern "C" {
 
 int zkref_threads(void) { return omp_get_max_threads(); }
+void zkref_set_threads(int n) { omp_set_dynamic(0); omp_set_num_threads(n > 0 ? n : 1); }
+
+// NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305) on an object built with the given extension
+void zkref_reverse_permutation(uint64_t *dst, uint64_t *src, uint64_t size, uint64_t offset_cols, uint64_t ncols, uint64_t ncols_all, int extension)
+{
+    NTT_Goldilocks ntt(size, 0, extension);
+    ntt.reversePermutation((E *)dst, (E *)src, size, offset_cols, ncols, ncols_all);
+}
+
+// One column strip of the row sponge, for pinning shapes whose extended trace does not fit host RAM as a whole: the loop
+// body of PoseidonGoldilocks::linear_hash (poseidon_goldilocks.cpp:240-256) over the reference's own hash_full_result,
+// with the running state[0..3] of row i kept in cap[4*i..] between strips ("capacity <- previous out[0..3]", :246-249).
+// Every strip but the last must be a multiple of RATE words so that the chunking equals the whole-row chunking.
+void zkref_sponge_absorb(uint64_t *cap, uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t nrows, int first)
+{
+#pragma omp parallel for
+    for (uint64_t i = 0; i < nrows; i++)
+    {
+        E state[SPONGE_WIDTH];
+        E *in = (E *)rows + i * row_ld;
+        if (first) memset(state + RATE, 0, CAPACITY * sizeof(E));
+        else std::memcpy(state + RATE, cap + 4 * i, CAPACITY * sizeof(E));
+        uint64_t remaining = strip_words;
+        while (remaining)
+        {
+            uint64_t n = (remaining < RATE) ? remaining : RATE;
+            memset(&state[n], 0, (RATE - n) * sizeof(E));
+            std::memcpy(state, in + (strip_words - remaining), n * sizeof(E));
+            PoseidonGoldilocks::hash_full_result(state, state);
+            remaining -= n;
+            if (remaining) std::memcpy(state + RATE, state, CAPACITY * sizeof(E));
+        }
+        std::memcpy(cap + 4 * i, state, CAPACITY * sizeof(E));
+    }
+}
+
+// Stage 4 of Starks::genProof (src/starkpil/starks.cpp:261-285) with the reference's own pieces:
+// nttExtended.INTT(qq1, q_2ns, NExt, qDim, NULL, 2, 1); the shift/regroup loop over Goldilocks3::mul(Element&, Element&,
+// Goldilocks::Element&) (goldilocks_cubic_extension.hpp:1887-1892); nttExtended.NTT(cm4_2ns, qq2, NExt, qDim*qDeg).
+// qq2 is a zero-initialised Polinomial(NExt*qDeg, qDim) (:233).  qDim must be 3 (Goldilocks3).
+void zkref_stage4(uint64_t *cm4_2ns, uint64_t *q_2ns, uint64_t n_ext, uint64_t n, uint64_t q_dim, uint64_t q_deg)
+{
+    NTT_Goldilocks nttExtended(n_ext);
+    Polinomial qq1(n_ext, q_dim);
+    Polinomial qq2(n_ext * q_deg, q_dim);
+    memset(qq2.address(), 0, n_ext * q_deg * q_dim * sizeof(E));
+    nttExtended.INTT(qq1.address(), (E *)q_2ns, n_ext, q_dim, NULL, 2, 1);
+    E shiftIn = Goldilocks::exp(Goldilocks::inv(Goldilocks::shift()), n);
+    uint64_t stride = 2048;
+#pragma omp parallel for
+    for (uint64_t ii = 0; ii < n; ii += stride)
+    {
+        E curS = Goldilocks::one();
+        for (uint64_t p = 0; p < q_deg; p++)
+        {
+            for (uint64_t k = ii; k < std::min(n, ii + stride); ++k)
+                Goldilocks3::mul((Goldilocks3::Element &)*qq2[k * q_deg + p], (Goldilocks3::Element &)*qq1[p * n + k], curS);
+            curS = Goldilocks::mul(curS, shiftIn);
+        }
+    }
+    nttExtended.NTT((E *)cm4_2ns, qq2.address(), n_ext, q_dim * q_deg);
+}
+
 
 // Goldilocks::toU64 (goldilocks_base_field_tools.hpp:152-163) over an array, in place.
 void zkref_canon(uint64_t *x, uint64_t n)

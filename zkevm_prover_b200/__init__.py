@@ -66,6 +66,13 @@ ABI_SYMBOLS = {
     "zkgpu_fri_transpose": (_int, [_vp, _vp, _u64, _u64]),
     "zkgpu_merkle_levels": (_int, [_vp, _u64]),
     "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
+    "zkgpu_init_multi": (_int, [_int]),
+    "zkgpu_nccl_unique_id": (_int, [_vp]),
+    "zkgpu_dist_init": (_int, [_vp, _int, _int]),
+    "zkgpu_dist_info": (_int, [ctypes.POINTER(_int), ctypes.POINTER(_int), ctypes.POINTER(_int)]),
+    "zkgpu_dist_plan": (_int, [_u64, _int, _int, ctypes.POINTER(_int), ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
+    "zkgpu_dist_commit": (_int, [_vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_u64), _int, _int, _u64, _u64, _u64]),
+    "zkgpu_dist_rows": (_int, [ctypes.POINTER(_vp), ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_vp)]),
 }
 
 

@@ -6,100 +6,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
-#include <mutex>
 #include <vector>
 
 namespace zk {
-
-unsigned long long g_launches = 0;
-static thread_local char g_err[512] = "";
-void set_error(const char *fmt, ...)
-{
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(g_err, sizeof(g_err), fmt, ap);
-    va_end(ap);
-}
-
-struct Ctx
-{
-    bool ready = false;
-    int device = 0;
-    cudaStream_t own = nullptr, cur = nullptr;
-    u64 *scratch = nullptr;
-    size_t scratch_words = 0;
-    cudaEvent_t ev[8] = {};
-    bool timed = false;
-    float stage[5] = {0, 0, 0, 0, 0};
-    // strip pipeline (commit_pipeline): copy streams, buffer hand-over events and per-strip timing segments
-    cudaStream_t h2d = nullptr, d2h = nullptr;
-    cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
-    std::vector<cudaEvent_t> pool; // timing events, grown on demand
-    struct Seg
-    {
-        int kind, a, b;
-    };
-    std::vector<Seg> segs; // segments of the last pipelined call: kind 0 = LDE, 1 = leaf absorption
-};
-static Ctx g_ctx;
-static std::recursive_mutex g_mu;
-
-static int ctx_init(int device)
-{
-    if (g_ctx.ready && (device < 0 || device == g_ctx.device)) return 0;
-    int n = 0;
-    cudaError_t e = cudaGetDeviceCount(&n);
-    if (e != cudaSuccess || n == 0)
-    {
-        cudaGetLastError();
-        set_error("zkgpu: no usable CUDA device (%s); this library has no CPU fallback",
-                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
-        return -3;
-    }
-    if (device >= 0) ZK_CUDA(cudaSetDevice(device));
-    ZK_CUDA(cudaGetDevice(&g_ctx.device));
-    cudaDeviceProp prop;
-    ZK_CUDA(cudaGetDeviceProperties(&prop, g_ctx.device));
-    if (prop.major < 10)
-    {
-        set_error("zkgpu: device %d is sm_%d%d; this build contains sm_100a code only", g_ctx.device, prop.major, prop.minor);
-        return -3;
-    }
-    if (!g_ctx.own) ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.own, cudaStreamNonBlocking));
-    if (!g_ctx.cur) g_ctx.cur = g_ctx.own;
-    for (auto &ev : g_ctx.ev)
-        if (!ev) ZK_CUDA(cudaEventCreate(&ev));
-    g_ctx.ready = true;
-    ZK_TRY(poseidon_init_constants());
-    return 0;
-}
-
-static int ensure_scratch(size_t words)
-{
-    if (words <= g_ctx.scratch_words) return 0;
-    if (g_ctx.scratch)
-    {
-        ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
-        ZK_CUDA(cudaFree(g_ctx.scratch));
-        g_ctx.scratch = nullptr;
-        g_ctx.scratch_words = 0;
-    }
-    ZK_CUDA(cudaMalloc(&g_ctx.scratch, words * sizeof(u64)));
-    g_ctx.scratch_words = words;
-    return 0;
-}
-
-static bool is_device_ptr(const void *p)
-{
-    if (!p) return false;
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess)
-    {
-        cudaGetLastError();
-        return false;
-    }
-    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
-}
 
 static inline bool is_pow2(u64 x) { return x && !(x & (x - 1)); }
 static inline unsigned ilog2(u64 x)
@@ -212,13 +121,13 @@ __global__ void field_op_kernel(int op, u64 *out, const u64 *a, const u64 *b, u6
 }
 
 // ---- LDE over all columns in strips that fit the scratch budget ----
-static int lde_all(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, unsigned log_n, unsigned log_b, u64 ncols, cudaStream_t st)
+static int lde_all(Ctx &C, u64 *out, u64 out_ld, const u64 *in, u64 in_ld, unsigned log_n, unsigned log_b, u64 ncols, cudaStream_t st)
 {
     if (ncols == 0) return 0;
     const u64 n = (u64)1 << log_n;
     size_t free_b = 0, total_b = 0;
     ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    free_b += g_ctx.scratch_words * sizeof(u64);
+    free_b += C.scratch_words * sizeof(u64);
     size_t budget = (size_t)(0.6 * (double)free_b);
     const size_t cap = (size_t)16 << 30;
     if (budget > cap) budget = cap;
@@ -234,11 +143,11 @@ static int lde_all(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, unsigned log_
             return -4;
         }
     }
-    ZK_TRY(ensure_scratch(2 * n * w));
+    ZK_TRY(ctx_ensure_scratch(C, 2 * n * w));
     for (u64 c0 = 0; c0 < ncols; c0 += w)
     {
         const u64 cw = ncols - c0 < w ? ncols - c0 : w;
-        ZK_TRY(lde_strip(out + c0, out_ld, in + c0, in_ld, g_ctx.scratch, log_n, log_b, cw, st));
+        ZK_TRY(lde_strip(out + c0, out_ld, in + c0, in_ld, C.scratch, log_n, log_b, cw, st));
     }
     return 0;
 }
@@ -282,51 +191,17 @@ struct Staged
 // Host-resident input / output strips are double buffered on the device and moved with strided 2-D copies on their
 // own streams; device-resident input / output is used in place.  The running leaf digests live in tree[0 .. 4*NExt).
 // ---------------------------------------------------------------------------------------------------
-static int pipe_event(int *idx, cudaStream_t st)
-{
-    static size_t used = 0;
-    if (idx == nullptr)
-    {
-        used = 0;
-        return 0;
-    }
-    if (used == g_ctx.pool.size())
-    {
-        cudaEvent_t e;
-        ZK_CUDA(cudaEventCreate(&e));
-        g_ctx.pool.push_back(e);
-    }
-    *idx = (int)used++;
-    ZK_CUDA(cudaEventRecord(g_ctx.pool[*idx], st));
-    return 0;
-}
-
-static int ensure_pipe_streams()
-{
-    if (g_ctx.h2d) return 0;
-    ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.h2d, cudaStreamNonBlocking));
-    ZK_CUDA(cudaStreamCreateWithFlags(&g_ctx.d2h, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; b++)
-    {
-        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_ready[b], cudaEventDisableTiming));
-        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.in_free[b], cudaEventDisableTiming));
-        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_ready[b], cudaEventDisableTiming));
-        ZK_CUDA(cudaEventCreateWithFlags(&g_ctx.out_free[b], cudaEventDisableTiming));
-    }
-    return 0;
-}
-
 // d_tree == nullptr: LDE only (extendPol with host pointers)
-static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *input, bool in_dev, unsigned log_n, unsigned log_b,
+static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *input, bool in_dev, unsigned log_n, unsigned log_b,
                            u64 ncols, cudaStream_t st)
 {
     const u64 n = (u64)1 << log_n, n_ext = n << log_b;
-    ZK_TRY(ensure_pipe_streams());
+    ZK_TRY(ctx_pipe_streams(C));
     // ---- strip width from the memory budget: per column 2n words of LDE scratch, 2n per host-input buffer pair,
     //      2*NExt per host-output buffer pair
     size_t free_b = 0, total_b = 0;
     ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    free_b += g_ctx.scratch_words * sizeof(u64);
+    free_b += C.scratch_words * sizeof(u64);
     size_t budget = (size_t)(0.6 * (double)free_b);
     const size_t cap = (size_t)24 << 30;
     if (budget > cap) budget = cap;
@@ -351,13 +226,13 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
         }
     }
     const u64 scratch_words = 2 * n * w, in_words = in_dev ? 0 : n * w, out_words = out_dev ? 0 : n_ext * w;
-    ZK_TRY(ensure_scratch(scratch_words + 2 * in_words + 2 * out_words));
-    u64 *lde_scratch = g_ctx.scratch;
-    u64 *in_buf[2] = {g_ctx.scratch + scratch_words, g_ctx.scratch + scratch_words + in_words};
-    u64 *out_buf[2] = {g_ctx.scratch + scratch_words + 2 * in_words, g_ctx.scratch + scratch_words + 2 * in_words + out_words};
+    ZK_TRY(ctx_ensure_scratch(C, scratch_words + 2 * in_words + 2 * out_words));
+    u64 *lde_scratch = C.scratch;
+    u64 *in_buf[2] = {C.scratch + scratch_words, C.scratch + scratch_words + in_words};
+    u64 *out_buf[2] = {C.scratch + scratch_words + 2 * in_words, C.scratch + scratch_words + 2 * in_words + out_words};
 
-    pipe_event(nullptr, st);
-    g_ctx.segs.clear();
+    ctx_pipe_event(C, nullptr, st);
+    C.segs.clear();
     // strip boundaries: full-width strips of w columns, except that with a host-resident trace the first strips ramp up
     // (16, 32, 48, 64 columns): only the copy of the first 16 columns is exposed and each later copy (1.33 ms per column)
     // nearly fits under the compute of the strip before it (2.0 ms per column).  Timelines (ZKGPU_PIPE_TRACE=1,
@@ -390,32 +265,32 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
     static const bool trace = getenv("ZKGPU_PIPE_TRACE") != nullptr;
     std::vector<std::pair<int, int>> h2d_ev;
     int t_origin = -1;
-    if (trace) ZK_TRY(pipe_event(&t_origin, st));
+    if (trace) ZK_TRY(ctx_pipe_event(C, &t_origin, st));
     auto issue_h2d = [&](u64 s) -> int {
         const int b = (int)(s & 1);
         const u64 cw = strip_cols(s);
-        if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[b], 0));
+        if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[b], 0));
         int t0 = -1, t1 = -1;
-        if (trace) ZK_TRY(pipe_event(&t0, g_ctx.h2d));
+        if (trace) ZK_TRY(ctx_pipe_event(C, &t0, C.h2d));
         ZK_CUDA(cudaMemcpy2DAsync(in_buf[b], cw * sizeof(u64), input + start[s], ncols * sizeof(u64), cw * sizeof(u64), n,
-                                  cudaMemcpyHostToDevice, g_ctx.h2d));
-        if (trace) ZK_TRY(pipe_event(&t1, g_ctx.h2d));
+                                  cudaMemcpyHostToDevice, C.h2d));
+        if (trace) ZK_TRY(ctx_pipe_event(C, &t1, C.h2d));
         if (trace) h2d_ev.push_back({t0, t1});
-        ZK_CUDA(cudaEventRecord(g_ctx.in_ready[b], g_ctx.h2d));
+        ZK_CUDA(cudaEventRecord(C.in_ready[b], C.h2d));
         return 0;
     };
     if (!in_dev)
     {
         // the copy stream must not start before work already queued on the compute stream (e.g. a previous call
         // still reading the staging buffers) has drained
-        ZK_CUDA(cudaEventRecord(g_ctx.in_free[0], st));
-        ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[0], 0));
+        ZK_CUDA(cudaEventRecord(C.in_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[0], 0));
         ZK_TRY(issue_h2d(0));
     }
     if (!out_dev)
     {
-        ZK_CUDA(cudaEventRecord(g_ctx.out_free[0], st));
-        ZK_CUDA(cudaStreamWaitEvent(g_ctx.d2h, g_ctx.out_free[0], 0));
+        ZK_CUDA(cudaEventRecord(C.out_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(C.d2h, C.out_free[0], 0));
     }
     for (u64 s = 0; s < nstrips; s++)
     {
@@ -426,7 +301,7 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
         if (!in_dev)
         {
             if (s + 1 < nstrips) ZK_TRY(issue_h2d(s + 1));
-            ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.in_ready[b], 0));
+            ZK_CUDA(cudaStreamWaitEvent(st, C.in_ready[b], 0));
             src = in_buf[b];
             src_ld = cw;
         }
@@ -434,47 +309,47 @@ static int commit_pipeline(u64 *out_ext, bool out_dev, u64 *d_tree, const u64 *i
         u64 dst_ld = ncols;
         if (!out_dev)
         {
-            if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[b], 0));
+            if (s >= 2) ZK_CUDA(cudaStreamWaitEvent(st, C.out_free[b], 0));
             dst = out_buf[b];
             dst_ld = cw;
         }
         int e0, e1, e2;
-        ZK_TRY(pipe_event(&e0, st));
+        ZK_TRY(ctx_pipe_event(C, &e0, st));
         ZK_TRY(lde_strip(dst, dst_ld, src, src_ld, lde_scratch, log_n, log_b, cw, st));
-        ZK_TRY(pipe_event(&e1, st));
-        if (!in_dev) ZK_CUDA(cudaEventRecord(g_ctx.in_free[b], st));
+        ZK_TRY(ctx_pipe_event(C, &e1, st));
+        if (!in_dev) ZK_CUDA(cudaEventRecord(C.in_free[b], st));
         if (d_tree) ZK_TRY(merkle_absorb(d_tree, dst, cw, dst_ld, n_ext, s == 0, st));
-        ZK_TRY(pipe_event(&e2, st));
-        g_ctx.segs.push_back({0, e0, e1});
-        g_ctx.segs.push_back({1, e1, e2});
+        ZK_TRY(ctx_pipe_event(C, &e2, st));
+        C.segs.push_back({0, e0, e1});
+        C.segs.push_back({1, e1, e2});
         if (!out_dev)
         {
-            ZK_CUDA(cudaEventRecord(g_ctx.out_ready[b], st));
-            ZK_CUDA(cudaStreamWaitEvent(g_ctx.d2h, g_ctx.out_ready[b], 0));
+            ZK_CUDA(cudaEventRecord(C.out_ready[b], st));
+            ZK_CUDA(cudaStreamWaitEvent(C.d2h, C.out_ready[b], 0));
             ZK_CUDA(cudaMemcpy2DAsync(out_ext + c0, ncols * sizeof(u64), out_buf[b], cw * sizeof(u64), cw * sizeof(u64), n_ext,
-                                      cudaMemcpyDeviceToHost, g_ctx.d2h));
-            ZK_CUDA(cudaEventRecord(g_ctx.out_free[b], g_ctx.d2h));
+                                      cudaMemcpyDeviceToHost, C.d2h));
+            ZK_CUDA(cudaEventRecord(C.out_free[b], C.d2h));
         }
     }
     if (!out_dev)
     {
         // the caller-visible completion point is the compute stream: make it wait for the last device->host strips
-        ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[0], 0));
-        ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[1], 0));
+        ZK_CUDA(cudaStreamWaitEvent(st, C.out_free[0], 0));
+        ZK_CUDA(cudaStreamWaitEvent(st, C.out_free[1], 0));
     }
     if (trace)
     {
         ZK_CUDA(cudaStreamSynchronize(st));
-        if (g_ctx.h2d) ZK_CUDA(cudaStreamSynchronize(g_ctx.h2d));
+        if (C.h2d) ZK_CUDA(cudaStreamSynchronize(C.h2d));
         auto at = [&](int e) {
             float ms = 0;
-            cudaEventElapsedTime(&ms, g_ctx.pool[t_origin], g_ctx.pool[e]);
+            cudaEventElapsedTime(&ms, C.pool[t_origin], C.pool[e]);
             return ms;
         };
         fprintf(stderr, "[zkgpu pipe] strip cols | h2d begin..end | lde begin..end | absorb end   (ms from call start)\n");
         for (u64 s = 0; s < nstrips; s++)
         {
-            const auto &l = g_ctx.segs[2 * s], &a = g_ctx.segs[2 * s + 1];
+            const auto &l = C.segs[2 * s], &a = C.segs[2 * s + 1];
             float hb = -1, he = -1;
             if (s < h2d_ev.size()) hb = at(h2d_ev[s].first), he = at(h2d_ev[s].second);
             fprintf(stderr, "[zkgpu pipe] %2llu %4llu | %8.1f %8.1f | %8.1f %8.1f | %8.1f\n", (unsigned long long)s,
@@ -541,34 +416,49 @@ __global__ void __launch_bounds__(256) fri_transpose_kernel(u64 *aux, const u64 
     aux[t] = pol[(j * w + i) * 3 + k];
 }
 
+
+// "device pointers only" entry points: reject host pointers and mis-aligned digest arrays (the kernels access leaves and
+// tree as 16-byte ulonglong2) with rc < 0 instead of a sticky device fault
+static int need_dev(const char *fn, const void *p, const char *what, bool align16)
+{
+    if (!is_device_ptr(p))
+    {
+        set_error("%s: %s must be a device pointer", fn, what);
+        return -1;
+    }
+    if (align16 && ((uintptr_t)p & 15))
+    {
+        set_error("%s: %s must be 16-byte aligned", fn, what);
+        return -1;
+    }
+    return 0;
+}
+
 } // namespace zk
 
 using namespace zk;
-#define LOCK std::lock_guard<std::recursive_mutex> lk__(g_mu)
-#define NEED_CTX ZK_TRY(ctx_init(-1))
 
 extern "C" {
 
 int zkgpu_init(int device)
 {
-    LOCK;
-    return ctx_init(device);
+    // device >= 0 binds the calling host thread to that device's context; -1 keeps the thread's (or the process default) one
+    zk::Enter en(device);
+    return en.rc;
 }
 int zkgpu_set_stream(void *s)
 {
-    LOCK;
-    NEED_CTX;
-    g_ctx.cur = (s == (void *)-1) ? g_ctx.own : (cudaStream_t)s; // 0 is the legacy default stream, a valid choice
+    ZK_ENTER;
+    C.cur = (s == (void *)-1) ? C.own : (cudaStream_t)s; // 0 is the legacy default stream, a valid choice
     return 0;
 }
 int zkgpu_sync(void)
 {
-    LOCK;
-    NEED_CTX;
-    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    ZK_ENTER;
+    ZK_CUDA(cudaStreamSynchronize(C.cur));
     return 0;
 }
-const char *zkgpu_last_error(void) { return g_err; }
+const char *zkgpu_last_error(void) { return last_error(); }
 uint64_t zkgpu_launch_count(void) { return g_launches; }
 int zkgpu_device_count(void)
 {
@@ -582,8 +472,7 @@ int zkgpu_device_count(void)
 }
 int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes)
 {
-    LOCK;
-    NEED_CTX;
+    ZK_ENTER;
     size_t f = 0, t = 0;
     ZK_CUDA(cudaMemGetInfo(&f, &t));
     if (free_bytes) *free_bytes = f;
@@ -592,88 +481,80 @@ int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes)
 }
 int zkgpu_malloc(void **p, uint64_t bytes)
 {
-    LOCK;
-    NEED_CTX;
+    ZK_ENTER;
     ZK_CUDA(cudaMalloc(p, bytes ? bytes : 8));
     return 0;
 }
 int zkgpu_free(void *p)
 {
-    LOCK;
-    NEED_CTX;
-    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    ZK_ENTER;
+    ZK_CUDA(cudaStreamSynchronize(C.cur));
     ZK_CUDA(cudaFree(p));
     return 0;
 }
 int zkgpu_malloc_host(void **p, uint64_t bytes)
 {
-    LOCK;
-    NEED_CTX;
+    ZK_ENTER;
     ZK_CUDA(cudaMallocHost(p, bytes ? bytes : 8));
     return 0;
 }
 int zkgpu_free_host(void *p)
 {
-    LOCK;
-    NEED_CTX;
+    ZK_ENTER;
     ZK_CUDA(cudaFreeHost(p));
     return 0;
 }
 int zkgpu_memcpy(void *dst, const void *src, uint64_t bytes)
 {
-    LOCK;
-    NEED_CTX;
-    ZK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, g_ctx.cur));
-    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    ZK_ENTER;
+    ZK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, C.cur));
+    ZK_CUDA(cudaStreamSynchronize(C.cur));
     return 0;
 }
 int zkgpu_stage_ms(float out[5])
 {
-    LOCK;
-    NEED_CTX;
-    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
-    if (g_ctx.timed && !g_ctx.segs.empty())
+    ZK_ENTER;
+    ZK_CUDA(cudaStreamSynchronize(C.cur));
+    if (C.timed && !C.segs.empty())
     {
-        g_ctx.stage[0] = g_ctx.stage[1] = 0;
-        for (const auto &sg : g_ctx.segs)
+        C.stage[0] = C.stage[1] = 0;
+        for (const auto &sg : C.segs)
         {
             float ms = 0;
-            ZK_CUDA(cudaEventElapsedTime(&ms, g_ctx.pool[sg.a], g_ctx.pool[sg.b]));
-            g_ctx.stage[sg.kind] += ms;
+            ZK_CUDA(cudaEventElapsedTime(&ms, C.pool[sg.a], C.pool[sg.b]));
+            C.stage[sg.kind] += ms;
         }
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[2], g_ctx.ev[2], g_ctx.ev[3]));
-        g_ctx.segs.clear();
-        g_ctx.timed = false;
+        ZK_CUDA(cudaEventElapsedTime(&C.stage[2], C.ev[2], C.ev[3]));
+        C.segs.clear();
+        C.timed = false;
     }
-    if (g_ctx.timed)
+    if (C.timed)
     {
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[0], g_ctx.ev[0], g_ctx.ev[1]));
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[1], g_ctx.ev[1], g_ctx.ev[2]));
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[2], g_ctx.ev[2], g_ctx.ev[3]));
-        g_ctx.timed = false;
+        ZK_CUDA(cudaEventElapsedTime(&C.stage[0], C.ev[0], C.ev[1]));
+        ZK_CUDA(cudaEventElapsedTime(&C.stage[1], C.ev[1], C.ev[2]));
+        ZK_CUDA(cudaEventElapsedTime(&C.stage[2], C.ev[2], C.ev[3]));
+        C.timed = false;
     }
-    for (int i = 0; i < 5; i++) out[i] = g_ctx.stage[i];
+    for (int i = 0; i < 5; i++) out[i] = C.stage[i];
     return 0;
 }
 int zkgpu_fill(uint64_t *dst, uint64_t n, uint64_t seed, uint64_t offset)
 {
-    LOCK;
-    NEED_CTX;
-    if (is_device_ptr(dst)) return fill_splitmix(dst, n, seed, offset, g_ctx.cur);
+    ZK_ENTER;
+    if (is_device_ptr(dst)) return fill_splitmix(dst, n, seed, offset, C.cur);
     Staged d;
     ZK_TRY(d.alloc(n));
-    ZK_TRY(fill_splitmix(d.d, n, seed, offset, g_ctx.cur));
-    ZK_CUDA(cudaMemcpyAsync(dst, d.d, n * sizeof(u64), cudaMemcpyDeviceToHost, g_ctx.cur));
-    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur));
+    ZK_TRY(fill_splitmix(d.d, n, seed, offset, C.cur));
+    ZK_CUDA(cudaMemcpyAsync(dst, d.d, n * sizeof(u64), cudaMemcpyDeviceToHost, C.cur));
+    ZK_CUDA(cudaStreamSynchronize(C.cur));
     return 0;
 }
 
 int zkgpu_field_op(int op, uint64_t *out, const uint64_t *a, const uint64_t *b, uint64_t n)
 {
-    LOCK;
     if (n == 0) return 0;
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     const bool dev = is_device_ptr(out);
     Staged da, db;
     const u64 *pa = a, *pb = b;
@@ -720,7 +601,6 @@ void zkgpu_ntt_destroy(void *h) { delete (NttHandle *)h; }
 
 int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, uint64_t *, int inverse, int extend)
 {
-    LOCK;
     if (size == 0 || ncols == 0) return 0; // ntt_goldilocks.cpp:168-171
     if (!is_pow2(size))
     {
@@ -732,10 +612,10 @@ int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_
         set_error("NTT: src is NULL");
         return -1;
     }
-    NEED_CTX;
+    ZK_ENTER;
     if (!dst) dst = const_cast<uint64_t *>(src);
     const unsigned L = ilog2(size);
-    cudaStream_t st = g_ctx.cur;
+    cudaStream_t st = C.cur;
     Scale pre, post;
     if (inverse)
     {
@@ -760,14 +640,14 @@ int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_
     const u64 words = size * ncols;
     if (dev)
     {
-        if (L > 8) ZK_TRY(ensure_scratch(words));
-        return ntt_transform(dst, ncols, src, ncols, g_ctx.scratch, L, ncols, inverse != 0, pre, post, st);
+        if (L > 8) ZK_TRY(ctx_ensure_scratch(C, words));
+        return ntt_transform(dst, ncols, src, ncols, C.scratch, L, ncols, inverse != 0, pre, post, st);
     }
     Staged d;
     ZK_TRY(d.alloc(words));
-    if (L > 8) ZK_TRY(ensure_scratch(words));
+    if (L > 8) ZK_TRY(ctx_ensure_scratch(C, words));
     ZK_CUDA(cudaMemcpyAsync(d.d, src, words * sizeof(u64), cudaMemcpyHostToDevice, st));
-    ZK_TRY(ntt_transform(d.d, ncols, d.d, ncols, g_ctx.scratch, L, ncols, inverse != 0, pre, post, st));
+    ZK_TRY(ntt_transform(d.d, ncols, d.d, ncols, C.scratch, L, ncols, inverse != 0, pre, post, st));
     ZK_CUDA(cudaMemcpyAsync(dst, d.d, words * sizeof(u64), cudaMemcpyDeviceToHost, st));
     ZK_CUDA(cudaStreamSynchronize(st));
     return 0;
@@ -776,7 +656,6 @@ int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_
 int zkgpu_reverse_permutation(void *h, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t offset_cols, uint64_t ncols,
                               uint64_t ncols_all)
 {
-    LOCK;
     if (size == 0 || ncols == 0) return 0;
     if (!is_pow2(size))
     {
@@ -790,8 +669,8 @@ int zkgpu_reverse_permutation(void *h, uint64_t *dst, const uint64_t *src, uint6
         set_error("reversePermutation: in place needs extension <= 1, offset_cols == 0 and ncols == ncols_all"); // :283, :302
         return -1;
     }
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     if (!dst) dst = const_cast<uint64_t *>(src);
     const unsigned L = ilog2(size);
     const bool dev = is_device_ptr(src);
@@ -852,27 +731,25 @@ static int check_lde_args(uint64_t n_ext, uint64_t n, unsigned *log_n, unsigned 
 int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64_t in_ld, uint64_t n_ext, uint64_t n,
                       uint64_t ncols)
 {
-    LOCK;
     if (n == 0 || ncols == 0) return 0;
     unsigned log_n, log_b;
     ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
-    NEED_CTX;
+    ZK_ENTER;
     if (!is_device_ptr(out) || !is_device_ptr(in))
     {
         set_error("zkgpu_lde_columns: device pointers required");
         return -1;
     }
-    return lde_all(out, out_ld, in, in_ld, log_n, log_b, ncols, g_ctx.cur);
+    return lde_all(C, out, out_ld, in, in_ld, log_n, log_b, ncols, C.cur);
 }
 
 int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n_ext, uint64_t n, uint64_t ncols, uint64_t *)
 {
-    LOCK;
     if (n == 0 || ncols == 0 || n_ext == 0) return 0;
     unsigned log_n, log_b;
     ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     const bool dev = is_device_ptr(input);
     if (dev != is_device_ptr(output))
     {
@@ -881,20 +758,20 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
     }
     if (dev)
     {
-        g_ctx.segs.clear();
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
-        ZK_TRY(lde_all(output, ncols, input, ncols, log_n, log_b, ncols, st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
-        g_ctx.timed = true;
+        C.segs.clear();
+        ZK_CUDA(cudaEventRecord(C.ev[0], st));
+        ZK_TRY(lde_all(C, output, ncols, input, ncols, log_n, log_b, ncols, st));
+        ZK_CUDA(cudaEventRecord(C.ev[1], st));
+        ZK_CUDA(cudaEventRecord(C.ev[2], st));
+        ZK_CUDA(cudaEventRecord(C.ev[3], st));
+        C.timed = true;
         return 0;
     }
     // host pointers: column strips, host->device of strip s+1 and device->host of strip s-1 overlap the LDE of strip s
-    ZK_TRY(commit_pipeline(output, false, nullptr, input, false, log_n, log_b, ncols, st));
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
-    g_ctx.timed = true;
+    ZK_TRY(commit_pipeline(C, output, false, nullptr, input, false, log_n, log_b, ncols, st));
+    ZK_CUDA(cudaEventRecord(C.ev[2], st));
+    ZK_CUDA(cudaEventRecord(C.ev[3], st));
+    C.timed = true;
     ZK_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
@@ -902,10 +779,9 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
 // ---------------------------------------------------------------------------------------------------
 int zkgpu_hash_full_result(uint64_t *out12, const uint64_t *in12, uint64_t n)
 {
-    LOCK;
     if (n == 0) return 0;
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     if (is_device_ptr(in12)) return poseidon_permute(out12, in12, n, st);
     Staged d;
     ZK_TRY(d.alloc(12 * n));
@@ -918,9 +794,8 @@ int zkgpu_hash_full_result(uint64_t *out12, const uint64_t *in12, uint64_t n)
 
 int zkgpu_linear_hash(uint64_t *out4, const uint64_t *input, uint64_t size)
 {
-    LOCK;
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     if (is_device_ptr(input)) return merkle_leaves(out4, input, size, size, 1, st);
     Staged d;
     ZK_TRY(d.alloc(size + 4));
@@ -940,8 +815,8 @@ static int merkletree_impl(uint64_t *tree, const uint64_t *input, uint64_t ncols
         set_error("merkletree: num_rows %llu is not a power of two", (unsigned long long)nrows);
         return -1;
     }
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     const u64 row_words = ncols * dim;
     const u64 tree_words = (2 * nrows - 1) * 4;
     const bool tree_dev = is_device_ptr(tree);
@@ -962,71 +837,68 @@ static int merkletree_impl(uint64_t *tree, const uint64_t *input, uint64_t ncols
         if (batched) return merkle_leaves_batch(leaves, rows, ncols, dim, batch, cnt, st);
         return merkle_leaves(leaves, rows, row_words, row_words, cnt, st);
     };
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
-    g_ctx.segs.clear();
+    ZK_CUDA(cudaEventRecord(C.ev[0], st));
+    ZK_CUDA(cudaEventRecord(C.ev[1], st));
+    C.segs.clear();
     if (in_dev)
         ZK_TRY(leaves_of(d_tree, input, nrows));
     else
     {
         // host rows: row chunks (~1 GiB), host->device copy of chunk k+1 overlaps the hashing of chunk k
-        ZK_TRY(ensure_pipe_streams());
+        ZK_TRY(ctx_pipe_streams(C));
         u64 chunk = ((u64)1 << 27) / row_words;
         if (chunk == 0) chunk = 1;
         if (chunk > nrows) chunk = nrows;
-        ZK_TRY(ensure_scratch(2 * chunk * row_words));
-        u64 *buf[2] = {g_ctx.scratch, g_ctx.scratch + chunk * row_words};
+        ZK_TRY(ctx_ensure_scratch(C, 2 * chunk * row_words));
+        u64 *buf[2] = {C.scratch, C.scratch + chunk * row_words};
         const u64 nchunks = (nrows + chunk - 1) / chunk;
         auto issue = [&](u64 k) -> int {
             const int b = (int)(k & 1);
             const u64 r0 = k * chunk, cnt = nrows - r0 < chunk ? nrows - r0 : chunk;
-            if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[b], 0));
-            ZK_CUDA(cudaMemcpyAsync(buf[b], input + r0 * row_words, cnt * row_words * sizeof(u64), cudaMemcpyHostToDevice, g_ctx.h2d));
-            ZK_CUDA(cudaEventRecord(g_ctx.in_ready[b], g_ctx.h2d));
+            if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[b], 0));
+            ZK_CUDA(cudaMemcpyAsync(buf[b], input + r0 * row_words, cnt * row_words * sizeof(u64), cudaMemcpyHostToDevice, C.h2d));
+            ZK_CUDA(cudaEventRecord(C.in_ready[b], C.h2d));
             return 0;
         };
-        ZK_CUDA(cudaEventRecord(g_ctx.in_free[0], st));
-        ZK_CUDA(cudaStreamWaitEvent(g_ctx.h2d, g_ctx.in_free[0], 0));
+        ZK_CUDA(cudaEventRecord(C.in_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[0], 0));
         ZK_TRY(issue(0));
         for (u64 k = 0; k < nchunks; k++)
         {
             const int b = (int)(k & 1);
             const u64 r0 = k * chunk, cnt = nrows - r0 < chunk ? nrows - r0 : chunk;
             if (k + 1 < nchunks) ZK_TRY(issue(k + 1));
-            ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.in_ready[b], 0));
+            ZK_CUDA(cudaStreamWaitEvent(st, C.in_ready[b], 0));
             ZK_TRY(leaves_of(d_tree + 4 * r0, buf[b], cnt));
-            ZK_CUDA(cudaEventRecord(g_ctx.in_free[b], st));
+            ZK_CUDA(cudaEventRecord(C.in_free[b], st));
         }
     }
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+    ZK_CUDA(cudaEventRecord(C.ev[2], st));
     ZK_TRY(merkle_levels(d_tree, nrows, st));
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
-    g_ctx.timed = true;
+    ZK_CUDA(cudaEventRecord(C.ev[3], st));
+    C.timed = true;
     if (!tree_dev) ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
     if (!tree_dev || !in_dev) ZK_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 int zkgpu_merkletree(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t dim)
 {
-    LOCK;
     return merkletree_impl(tree, input, ncols, nrows, 0, dim, false);
 }
 int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t batch, uint64_t dim)
 {
-    LOCK;
     return merkletree_impl(tree, input, ncols, nrows, batch, dim, true);
 }
 
 int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *nodes, uint64_t width, uint64_t height, uint64_t idx)
 {
-    LOCK;
     if (height == 0 || idx >= height)
     {
         set_error("getGroupProof: idx %llu out of range (height %llu)", (unsigned long long)idx, (unsigned long long)height);
         return -1;
     }
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     const unsigned levels = ilog2(height);
     const u64 proof_words = width + 4 * (u64)levels;
     const bool src_dev = width == 0 || is_device_ptr(source), nodes_dev = levels == 0 || is_device_ptr(nodes), proof_dev = is_device_ptr(proof);
@@ -1074,49 +946,57 @@ int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *n
 
 int zkgpu_merkle_leaves(uint64_t *leaves, const uint64_t *rows, uint64_t row_words, uint64_t row_ld, uint64_t nrows)
 {
-    LOCK;
-    NEED_CTX;
-    return merkle_leaves(leaves, rows, row_words, row_ld, nrows, g_ctx.cur);
+    ZK_ENTER;
+    if (nrows == 0) return 0;
+    ZK_TRY(need_dev("merkle_leaves", leaves, "leaves", true));
+    if (row_words) ZK_TRY(need_dev("merkle_leaves", rows, "rows", false));
+    return merkle_leaves(leaves, rows, row_words, row_ld, nrows, C.cur);
 }
 int zkgpu_merkle_absorb(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t nrows, int first)
 {
-    LOCK;
-    NEED_CTX;
-    return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, g_ctx.cur);
+    ZK_ENTER;
+    if (nrows == 0 || strip_words == 0) return 0;
+    ZK_TRY(need_dev("merkle_absorb", leaves, "leaves", true));
+    ZK_TRY(need_dev("merkle_absorb", rows, "rows", false));
+    return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, C.cur);
 }
 int zkgpu_merkle_absorb_copy(uint64_t *leaves, const uint64_t *rows, uint64_t strip_words, uint64_t row_ld, uint64_t nrows, int first,
                              uint64_t *copy_to, uint64_t copy_ld)
 {
-    LOCK;
-    NEED_CTX;
+    ZK_ENTER;
     if (!copy_to)
     {
         set_error("merkle_absorb_copy: null destination");
         return -1;
     }
-    return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, g_ctx.cur, copy_to, copy_ld);
+    if (nrows == 0 || strip_words == 0) return 0;
+    ZK_TRY(need_dev("merkle_absorb_copy", leaves, "leaves", true));
+    ZK_TRY(need_dev("merkle_absorb_copy", rows, "rows", false));
+    ZK_TRY(need_dev("merkle_absorb_copy", copy_to, "copy_to", false));
+    return merkle_absorb(leaves, rows, strip_words, row_ld, nrows, first != 0, C.cur, copy_to, copy_ld);
 }
 int zkgpu_merkle_levels(uint64_t *tree, uint64_t nrows)
 {
-    LOCK;
     if (nrows == 0) return 0;
     if (!is_pow2(nrows))
     {
         set_error("merkle_levels: num_rows %llu is not a power of two", (unsigned long long)nrows);
         return -1;
     }
-    NEED_CTX;
-    return merkle_levels(tree, nrows, g_ctx.cur);
+    ZK_ENTER;
+    ZK_TRY(need_dev("merkle_levels", tree, "tree", true));
+    return merkle_levels(tree, nrows, C.cur);
 }
 int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64_t src_ld, uint64_t nrows, uint64_t ncols)
 {
-    LOCK;
-    NEED_CTX;
+    ZK_ENTER;
     const u64 total = nrows * ncols;
     if (total == 0) return 0;
+    ZK_TRY(need_dev("copy_block", dst, "dst", false));
+    ZK_TRY(need_dev("copy_block", src, "src", false));
     u64 blocks = (total + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
-    copy_block_kernel<<<(unsigned)blocks, 256, 0, g_ctx.cur>>>(dst, dst_ld, src, src_ld, nrows, ncols);
+    copy_block_kernel<<<(unsigned)blocks, 256, 0, C.cur>>>(dst, dst_ld, src, src_ld, nrows, ncols);
     ZK_LAUNCHED();
     ZK_CUDA(cudaGetLastError());
     return 0;
@@ -1126,12 +1006,14 @@ int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64
 int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const uint64_t *input, uint64_t n_ext, uint64_t n,
                                uint64_t ncols)
 {
-    LOCK;
     if (n == 0 || n_ext == 0) return 0;
     unsigned log_n, log_b;
     ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    // after zkgpu_init_multi a host-resident trace is committed by all GPUs of the job (dist.cu)
+    if (dist_world_of_process() > 1 && ncols > 0 && !is_device_ptr(input) && n_ext >= (u64)dist_world_of_process())
+        return dist_multi_commit(out_ext, tree, input, n_ext, n, ncols);
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     // each pointer may independently be host or device: e.g. host trace in, extended trace kept resident on the
     // device (what getGroupProof / stage 4 need later), tree back on the host.
     const bool in_dev = ncols == 0 || is_device_ptr(input);
@@ -1151,7 +1033,7 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
         ZK_TRY(dtree.alloc(tree_words));
         d_tree = dtree.d;
     }
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[4], st));
+    ZK_CUDA(cudaEventRecord(C.ev[4], st));
     if (ncols <= 4)
     {
         // rows of <= 4 words are copied, not hashed (poseidon_goldilocks.cpp:234-239): no sponge to pipeline
@@ -1169,49 +1051,48 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
             ZK_TRY(dout.alloc(n_ext * ncols));
             d_out = dout.d;
         }
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[0], st));
-        ZK_TRY(lde_all(d_out, ncols, d_in, ncols, log_n, log_b, ncols, st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[1], st));
-        ZK_TRY(merkle_all(d_tree, d_out, ncols, n_ext, st, g_ctx.ev[2]));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
-        g_ctx.segs.clear();
+        ZK_CUDA(cudaEventRecord(C.ev[0], st));
+        ZK_TRY(lde_all(C, d_out, ncols, d_in, ncols, log_n, log_b, ncols, st));
+        ZK_CUDA(cudaEventRecord(C.ev[1], st));
+        ZK_TRY(merkle_all(d_tree, d_out, ncols, n_ext, st, C.ev[2]));
+        ZK_CUDA(cudaEventRecord(C.ev[3], st));
+        C.segs.clear();
         if (!out_dev) ZK_CUDA(cudaMemcpyAsync(out_ext, d_out, n_ext * ncols * sizeof(u64), cudaMemcpyDeviceToHost, st));
         if (!out_dev || !in_dev) ZK_CUDA(cudaStreamSynchronize(st));
     }
     else
     {
-        ZK_TRY(commit_pipeline(out_ext, out_dev, d_tree, input, in_dev, log_n, log_b, ncols, st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[2], st));
+        ZK_TRY(commit_pipeline(C, out_ext, out_dev, d_tree, input, in_dev, log_n, log_b, ncols, st));
+        ZK_CUDA(cudaEventRecord(C.ev[2], st));
         if (!tree_dev)
         {
             // the leaf level (half of the tree) goes back to the host while the node levels are hashed
-            ZK_CUDA(cudaStreamWaitEvent(g_ctx.d2h, g_ctx.ev[2], 0));
-            ZK_CUDA(cudaMemcpyAsync(tree, d_tree, n_ext * 4 * sizeof(u64), cudaMemcpyDeviceToHost, g_ctx.d2h));
-            ZK_CUDA(cudaEventRecord(g_ctx.out_free[0], g_ctx.d2h));
+            ZK_CUDA(cudaStreamWaitEvent(C.d2h, C.ev[2], 0));
+            ZK_CUDA(cudaMemcpyAsync(tree, d_tree, n_ext * 4 * sizeof(u64), cudaMemcpyDeviceToHost, C.d2h));
+            ZK_CUDA(cudaEventRecord(C.out_free[0], C.d2h));
             leaves_sent = n_ext * 4;
         }
         ZK_TRY(merkle_levels(d_tree, n_ext, st));
-        ZK_CUDA(cudaEventRecord(g_ctx.ev[3], st));
+        ZK_CUDA(cudaEventRecord(C.ev[3], st));
     }
-    g_ctx.timed = true;
+    C.timed = true;
     if (!tree_dev)
     {
         ZK_CUDA(cudaMemcpyAsync(tree + leaves_sent, d_tree + leaves_sent, (tree_words - leaves_sent) * sizeof(u64), cudaMemcpyDeviceToHost, st));
-        if (leaves_sent) ZK_CUDA(cudaStreamWaitEvent(st, g_ctx.out_free[0], 0));
+        if (leaves_sent) ZK_CUDA(cudaStreamWaitEvent(st, C.out_free[0], 0));
     }
-    ZK_CUDA(cudaEventRecord(g_ctx.ev[5], st));
+    ZK_CUDA(cudaEventRecord(C.ev[5], st));
     if (!in_dev || !out_dev || !tree_dev)
     {
         ZK_CUDA(cudaStreamSynchronize(st));
-        g_ctx.stage[3] = 0;
-        ZK_CUDA(cudaEventElapsedTime(&g_ctx.stage[4], g_ctx.ev[4], g_ctx.ev[5])); // whole call on the device clock
+        C.stage[3] = 0;
+        ZK_CUDA(cudaEventElapsedTime(&C.stage[4], C.ev[4], C.ev[5])); // whole call on the device clock
     }
     return 0;
 }
 
 int zkgpu_tune(int key, int value)
 {
-    LOCK;
     switch (key)
     {
     case 0: g_absorb_threads = value == 512 ? 512 : 128; return 0;
@@ -1223,24 +1104,22 @@ int zkgpu_tune(int key, int value)
 
 int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t n_bits, uint64_t n_bits_ext, uint64_t n_pols)
 {
-    LOCK;
     if (n_bits > 32 || n_bits_ext > 32 || n_bits_ext < n_bits || !image)
     {
         set_error("buildConstTree: need nBits <= nBitsExt <= 32 and an image buffer");
         return -1;
     }
-    NEED_CTX;
+    ZK_ENTER;
     const u64 n = (u64)1 << n_bits, n_ext = (u64)1 << n_bits_ext;
     const u64 header[2] = {n_pols, n_ext}; // constTree[0] = nPols, constTree[1] = nExt (build_const_tree.cpp:576-577)
-    ZK_CUDA(cudaMemcpyAsync(image, header, sizeof(header), cudaMemcpyDefault, g_ctx.cur));
-    ZK_CUDA(cudaStreamSynchronize(g_ctx.cur)); // header[] is a stack buffer
+    ZK_CUDA(cudaMemcpyAsync(image, header, sizeof(header), cudaMemcpyDefault, C.cur));
+    ZK_CUDA(cudaStreamSynchronize(C.cur)); // header[] is a stack buffer
     return zkgpu_extend_and_merkelize(nullptr, image + 2, image + 2 + n_pols * n_ext, const_pols, n_ext, n, n_pols);
 }
 
 int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits, uint64_t next_bits, uint64_t shift_inv,
                    const uint64_t *special_x)
 {
-    LOCK;
     if (!pol2_e || !fri_pol || !special_x)
     {
         set_error("fri_fold: NULL argument");
@@ -1251,8 +1130,8 @@ int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits,
         set_error("fri_fold: need next_bits <= pol_bits <= 32 (got %llu, %llu)", (unsigned long long)next_bits, (unsigned long long)pol_bits);
         return -1;
     }
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     const u64 pol2n = (u64)1 << next_bits, nx = (u64)1 << (pol_bits - next_bits), words_in = ((u64)3 << pol_bits), words_out = pol2n * 3;
     const bool dev = is_device_ptr(fri_pol);
     if (dev != is_device_ptr(pol2_e))
@@ -1266,8 +1145,8 @@ int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits,
     // every group's INTT at once: ppar[i] = friPol[i*pol2N + g] is row i, columns 3g..3g+2 of an nX x 3 pol2N matrix.
     // The coefficients live in the library's scratch area (followed by the transform's own scratch for nX > 256).
     const unsigned L = ilog2(nx);
-    ZK_TRY(ensure_scratch(words_in * (L > 8 ? 2 : 1)));
-    u64 *coef = g_ctx.scratch;
+    ZK_TRY(ctx_ensure_scratch(C, words_in * (L > 8 ? 2 : 1)));
+    u64 *coef = C.scratch;
     if (!dev)
     {
         ZK_TRY(in.alloc(words_in));
@@ -1282,7 +1161,7 @@ int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits,
         post.mode = SCALE_CONST;
         post.konst = gl::pow_slow(nx % GL_P, GL_P - 2);
     }
-    ZK_TRY(ntt_transform(coef, words_out, d_in, words_out, g_ctx.scratch + words_in, L, words_out, true, pre, post, st));
+    ZK_TRY(ntt_transform(coef, words_out, d_in, words_out, C.scratch + words_in, L, words_out, true, pre, post, st));
     const u64 wi = gl::pow_slow(gl::root_of_unity((unsigned)pol_bits), GL_P - 2); // Goldilocks::inv(Goldilocks::w(polBits)), friProve.cpp:36
     fri_fold_kernel<<<nblocks(pol2n, 256), 256, 0, st>>>(d_out, coef, nx, pol2n, shift_inv % GL_P, wi, special_x[0] % GL_P,
                                                          special_x[1] % GL_P, special_x[2] % GL_P);
@@ -1298,7 +1177,6 @@ int zkgpu_fri_fold(uint64_t *pol2_e, const uint64_t *fri_pol, uint64_t pol_bits,
 
 int zkgpu_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint64_t transpose_bits)
 {
-    LOCK;
     if (degree == 0) return 0;
     if (!aux || !pol || aux == pol)
     {
@@ -1311,8 +1189,8 @@ int zkgpu_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, uin
         set_error("fri_transpose: degree %llu is not a multiple of 2^%llu", (unsigned long long)degree, (unsigned long long)transpose_bits);
         return -1;
     }
-    NEED_CTX;
-    cudaStream_t st = g_ctx.cur;
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
     const u64 h = degree / w, words = degree * 3;
     const bool dev = is_device_ptr(pol);
     if (dev != is_device_ptr(aux))

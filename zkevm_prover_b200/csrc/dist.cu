@@ -1,0 +1,812 @@
+// dist.cu — the commit stage sharded over the GPUs of one box, behind the C ABI (include/zkgpu.h: zkgpu_init_multi,
+// zkgpu_dist_init, zkgpu_dist_commit; zkgpu_extend_and_merkelize dispatches here after zkgpu_init_multi).
+//
+// Reference call pair: ntt.extendPol(...) + treesGL[k]->merkelize() in Starks::genProof (src/starkpil/starks.cpp:51-58),
+// one process, one proof in flight (src/prover/prover.cpp:182-221).  The split follows the data dependences of the
+// reference code: the LDE is independent per column (ntt_goldilocks.cpp:103-110) -> column pieces; the leaf sponge
+// needs whole rows in column order (poseidon_goldilocks.cpp:277-281) -> row shards; node levels are independent per
+// subtree below the top log2(G) levels (:283-300).
+//
+//   rank g, round k:   [host->device of piece k+1]  ||  LDE of piece (k, g): the LAST PASS of every coset transform stores
+//                      each extended row straight into the row shard of the rank that owns it — its own memory or a
+//                      peer's over NVLink (ntt_tile.cuh: scatter output) — so the column-shard -> row-shard exchange is
+//                      done by the transform's own stores, tile by tile, under the arithmetic of the next tile
+//                      ||  sponge absorption of the columns of round k-1 on this rank's rows
+//   then: subtree levels per rank, sub-roots all-gathered, top log2(G) levels on rank 0, levels stitched into the
+//   reference's level-major node array.
+//
+// NCCL (dlopen'ed, no link-time dependency) provides the rendezvous, the cross-GPU stream barriers (1-word all-reduce),
+// the exchange of CUDA IPC handles in the process-per-GPU form, the sub-root all-gather and the level stitch.  When
+// peer access is unavailable (or ZKGPU_EXCHANGE=nccl) the exchange falls back to grouped ncclSend/ncclRecv per round.
+#include "gl64.cuh"
+#include "zk_internal.h"
+#include "../../include/zkgpu.h"
+#include <nccl.h>
+#include <dlfcn.h>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+
+namespace zk {
+
+// ---------------------------------------------------------------------------------------------------
+// NCCL through dlopen: the process may already hold a libnccl.so.2 (torch bundles one); share it
+// ---------------------------------------------------------------------------------------------------
+struct NcclApi
+{
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetVersion)(int *) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+
+static int nccl_load()
+{
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.h) return 0;
+    void *h = nullptr;
+    if (const char *p = getenv("ZKGPU_NCCL_LIB")) h = dlopen(p, RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h)
+    {
+        set_error("zkgpu: cannot load NCCL (libnccl.so.2): %s", dlerror());
+        return -5;
+    }
+#define ZK_SYM(name)                                                        \
+    *(void **)(&g_nccl.name) = dlsym(h, "nccl" #name);                      \
+    if (!g_nccl.name)                                                       \
+    {                                                                       \
+        set_error("zkgpu: NCCL symbol nccl" #name " not found");            \
+        return -5;                                                          \
+    }
+    ZK_SYM(GetUniqueId) ZK_SYM(CommInitRank) ZK_SYM(CommInitAll) ZK_SYM(CommDestroy) ZK_SYM(AllReduce) ZK_SYM(AllGather)
+    ZK_SYM(Send) ZK_SYM(Recv) ZK_SYM(GroupStart) ZK_SYM(GroupEnd) ZK_SYM(GetErrorString) ZK_SYM(GetVersion)
+#undef ZK_SYM
+    g_nccl.h = h;
+    return 0;
+}
+#define ZK_NCCL(call)                                                                                       \
+    do {                                                                                                    \
+        ncclResult_t r__ = (call);                                                                          \
+        if (r__ != ncclSuccess) {                                                                           \
+            zk::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r__));         \
+            return -5;                                                                                      \
+        }                                                                                                   \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------------
+// state
+// ---------------------------------------------------------------------------------------------------
+static const int MAX_WORLD = 16, MAX_ROUNDS = 16;
+
+struct Dist
+{
+    int rank = 0, world = 1;
+    bool single_process = false;
+    bool p2p = false, p2p_tried = false;
+    ncclComm_t comm = nullptr;
+    cudaStream_t cs = nullptr; // every NCCL operation of this rank is issued here
+    cudaEvent_t ev_lde[MAX_ROUNDS] = {}, ev_bar[MAX_ROUNDS] = {}, ev_unp[MAX_ROUNDS] = {}, ev_a = nullptr, ev_b = nullptr;
+    u64 *flag = nullptr;                                   // barrier word
+    u64 *rows = nullptr;                                   // this rank's row shard of the extended trace, R x ncols
+    size_t rows_cap = 0;                                   // words allocated
+    u64 rows_n = 0, rows_c = 0;                            // shape of the last commit
+    u64 *peer_rows[MAX_WORLD] = {};                        // every rank's shard as seen from this device
+    void *ipc_open[MAX_WORLD] = {};                        // IPC mappings to close on reallocation
+    u64 *peer_tab = nullptr;                               // device copy of peer_rows
+    u64 *sub = nullptr;                                    // subtree over this rank's R leaves
+    size_t sub_cap = 0;
+    u64 *top = nullptr;                                    // (2*world - 1) * 4 words: levels above the sub-roots
+    u64 *tree_dev = nullptr;                               // rank 0, host tree pointer, process-per-GPU: staging
+    size_t tree_cap = 0;
+    u64 *in_buf = nullptr;                                 // host-input staging, two slots
+    size_t in_cap = 0;
+    u64 *ext_buf = nullptr, *recv_buf = nullptr;           // fallback exchange (no peer access)
+    size_t ext_cap = 0, recv_cap = 0;
+    u64 *ipc_scratch = nullptr;                            // world * 64 bytes for the handle all-gather
+};
+
+// the ranks of a single-process job (zkgpu_init_multi): worker threads meet here
+struct Group
+{
+    int n = 0;
+    Ctx *ctx[MAX_WORLD] = {};
+    std::mutex mu;
+    std::condition_variable cv;
+    int arrived = 0;
+    unsigned long long phase = 0;
+    u64 *shared_rows[MAX_WORLD] = {};
+    int shared_rc[MAX_WORLD] = {};
+    void barrier()
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        const unsigned long long ph = phase;
+        if (++arrived == n)
+        {
+            arrived = 0;
+            phase++;
+            cv.notify_all();
+        }
+        else
+            cv.wait(lk, [&] { return phase != ph; });
+    }
+};
+static Group g_group;
+
+static int dev_realloc(u64 **p, size_t *cap, size_t words)
+{
+    if (words <= *cap && *p) return 0;
+    if (*p) ZK_CUDA(cudaFree(*p));
+    *p = nullptr;
+    *cap = 0;
+    cudaError_t e = cudaMalloc(p, (words ? words : 1) * sizeof(u64));
+    if (e != cudaSuccess)
+    {
+        cudaGetLastError();
+        set_error("zkgpu dist: cannot allocate %llu MiB on the device (%s)", (unsigned long long)(words >> 17), cudaGetErrorString(e));
+        return -4;
+    }
+    *cap = words;
+    return 0;
+}
+
+static int dist_create(Ctx &C, int rank, int world, ncclComm_t comm, bool single)
+{
+    Dist *D = new Dist();
+    D->rank = rank;
+    D->world = world;
+    D->comm = comm;
+    D->single_process = single;
+    ZK_CUDA(cudaStreamCreateWithFlags(&D->cs, cudaStreamNonBlocking));
+    for (int i = 0; i < MAX_ROUNDS; i++)
+    {
+        ZK_CUDA(cudaEventCreateWithFlags(&D->ev_lde[i], cudaEventDisableTiming));
+        ZK_CUDA(cudaEventCreateWithFlags(&D->ev_bar[i], cudaEventDisableTiming));
+        ZK_CUDA(cudaEventCreateWithFlags(&D->ev_unp[i], cudaEventDisableTiming));
+    }
+    ZK_CUDA(cudaEventCreateWithFlags(&D->ev_a, cudaEventDisableTiming));
+    ZK_CUDA(cudaEventCreateWithFlags(&D->ev_b, cudaEventDisableTiming));
+    ZK_CUDA(cudaMalloc(&D->flag, 64));
+    ZK_CUDA(cudaMemset(D->flag, 0, 64));
+    ZK_CUDA(cudaMalloc(&D->peer_tab, MAX_WORLD * sizeof(u64)));
+    ZK_CUDA(cudaMalloc(&D->top, (2 * (size_t)world - 1) * 4 * sizeof(u64)));
+    ZK_CUDA(cudaMalloc(&D->ipc_scratch, (size_t)world * 64));
+    C.dist = D;
+    return 0;
+}
+
+// all ranks have finished everything enqueued on `after` before anything enqueued later on `then` starts
+static int dist_barrier(Dist &D, cudaStream_t after, cudaStream_t then, cudaEvent_t e_in, cudaEvent_t e_out)
+{
+    ZK_CUDA(cudaEventRecord(e_in, after));
+    ZK_CUDA(cudaStreamWaitEvent(D.cs, e_in, 0));
+    ZK_NCCL(g_nccl.AllReduce(D.flag, D.flag + 1, 1, ncclUint64, ncclSum, D.comm, D.cs));
+    ZK_CUDA(cudaEventRecord(e_out, D.cs));
+    if (then) ZK_CUDA(cudaStreamWaitEvent(then, e_out, 0));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// column ownership: the row is cut into rounds x world consecutive pieces, piece (k, g) belonging to rank g in round k.
+// Every round but the last covers a whole number of 8-column sponge blocks (so absorbing round by round chunks the row
+// exactly as linear_hash does, poseidon_goldilocks.cpp:240-256); inside a round the columns are dealt out evenly.
+// Device-resident input: one round (nothing to hide, widest pieces).  Host input: the rounds ramp up (2 blocks per rank,
+// 4, then rounds of at most 8) so that only the copy of the first small piece is exposed.
+// ---------------------------------------------------------------------------------------------------
+struct Plan
+{
+    int rounds = 0, world = 1;
+    u64 c0[MAX_ROUNDS][MAX_WORLD], w[MAX_ROUNDS][MAX_WORLD];
+    u64 round_c0[MAX_ROUNDS], round_w[MAX_ROUNDS];
+};
+
+static int make_plan(Plan &pl, u64 ncols, int world, bool host_input)
+{
+    pl.world = world;
+    const u64 blocks = (ncols + 7) / 8;
+    u64 per_round[MAX_ROUNDS];
+    int nr = 0;
+    if (!host_input || blocks == 0)
+        per_round[nr++] = blocks;
+    else
+    {
+        u64 left = blocks;
+        const u64 wants[2] = {2 * (u64)world, 4 * (u64)world};
+        for (u64 want : wants)
+            if (left >= want + 4 * (u64)world)
+            {
+                per_round[nr++] = want;
+                left -= want;
+            }
+        u64 k = (left + 8 * (u64)world - 1) / (8 * (u64)world);
+        if (k < 1) k = 1;
+        if (k > (u64)(MAX_ROUNDS - nr)) k = MAX_ROUNDS - nr;
+        for (u64 i = 0; i < k; i++) per_round[nr++] = left / k + (i < left % k ? 1 : 0);
+    }
+    pl.rounds = nr;
+    u64 c = 0;
+    int rot = 0;
+    for (int k = 0; k < nr; k++)
+    {
+        u64 cols = per_round[k] * 8;
+        if (cols > ncols - c) cols = ncols - c;
+        pl.round_c0[k] = c;
+        pl.round_w[k] = cols;
+        const u64 base = cols / world, extra = cols % world;
+        for (int g = 0; g < world; g++)
+        {
+            // the odd columns of a round go to a different group of ranks each round, so that column counts stay level
+            const u64 wg = base + ((u64)((g - rot + world) % world) < extra ? 1 : 0);
+            pl.c0[k][g] = c;
+            pl.w[k][g] = wg;
+            c += wg;
+        }
+        rot = (int)((rot + extra) % world);
+    }
+    return 0;
+}
+
+static int subtree_levels(u64 leaves, u64 *off, u64 *cnt)
+{
+    int l = 0;
+    u64 o = 0, n = leaves;
+    for (;;)
+    {
+        off[l] = o;
+        cnt[l] = n;
+        l++;
+        if (n == 1) break;
+        o += n * 4;
+        n >>= 1;
+    }
+    return l;
+}
+
+// (re)allocate this rank's row shard and learn where every peer's shard is.  Collective: every rank calls it with the
+// same shape.  grp != nullptr: ranks are threads of this process.
+static int dist_setup_rows(Ctx &C, Dist &D, u64 need_words)
+{
+    static const bool force_nccl = []() { const char *e = getenv("ZKGPU_EXCHANGE"); return e && !strcmp(e, "nccl"); }();
+    if (D.rows && need_words <= D.rows_cap && D.p2p_tried) return 0;
+    ZK_CUDA(cudaStreamSynchronize(C.cur));
+    ZK_CUDA(cudaStreamSynchronize(D.cs));
+    if (!D.single_process)
+        for (int g = 0; g < D.world; g++)
+            if (D.ipc_open[g])
+            {
+                cudaIpcCloseMemHandle(D.ipc_open[g]);
+                D.ipc_open[g] = nullptr;
+            }
+    ZK_TRY(dev_realloc(&D.rows, &D.rows_cap, need_words));
+    for (int g = 0; g < D.world; g++) D.peer_rows[g] = nullptr;
+    D.peer_rows[D.rank] = D.rows;
+    bool ok = !force_nccl;
+    if (D.single_process)
+    {
+        g_group.shared_rows[D.rank] = D.rows;
+        g_group.barrier();
+        for (int g = 0; g < D.world; g++) D.peer_rows[g] = g_group.shared_rows[g];
+        if (ok)
+            for (int g = 0; g < D.world && ok; g++)
+                if (g != D.rank)
+                {
+                    int can = 0;
+                    if (cudaDeviceCanAccessPeer(&can, C.device, g_group.ctx[g]->device) != cudaSuccess || !can) ok = false;
+                }
+        g_group.shared_rc[D.rank] = ok ? 1 : 0;
+        g_group.barrier();
+        for (int g = 0; g < D.world; g++) ok = ok && g_group.shared_rc[g];
+        g_group.barrier(); // shared_* may be rewritten by the next call only after everyone has read them
+    }
+    else
+    {
+        cudaIpcMemHandle_t mine, all[MAX_WORLD];
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+        memset(&mine, 0, sizeof(mine));
+        if (ok && cudaIpcGetMemHandle(&mine, D.rows) != cudaSuccess)
+        {
+            cudaGetLastError();
+            ok = false;
+        }
+        ZK_CUDA(cudaMemcpyAsync((char *)D.ipc_scratch + 64 * D.rank, &mine, 64, cudaMemcpyHostToDevice, D.cs));
+        ZK_NCCL(g_nccl.AllGather((char *)D.ipc_scratch + 64 * D.rank, D.ipc_scratch, 64, ncclChar, D.comm, D.cs));
+        ZK_CUDA(cudaMemcpyAsync(all, D.ipc_scratch, 64 * (size_t)D.world, cudaMemcpyDeviceToHost, D.cs));
+        ZK_CUDA(cudaStreamSynchronize(D.cs));
+        for (int g = 0; g < D.world && ok; g++)
+            if (g != D.rank)
+            {
+                void *p = nullptr;
+                if (cudaIpcOpenMemHandle(&p, all[g], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+                {
+                    cudaGetLastError();
+                    ok = false;
+                    break;
+                }
+                D.ipc_open[g] = p;
+                D.peer_rows[g] = (u64 *)p;
+            }
+        // everyone must take the same path: sum of the failure flags
+        const u64 bad = ok ? 0 : 1;
+        ZK_CUDA(cudaMemcpyAsync(D.flag + 2, &bad, 8, cudaMemcpyHostToDevice, D.cs));
+        ZK_NCCL(g_nccl.AllReduce(D.flag + 2, D.flag + 3, 1, ncclUint64, ncclSum, D.comm, D.cs));
+        u64 total_bad = 0;
+        ZK_CUDA(cudaMemcpyAsync(&total_bad, D.flag + 3, 8, cudaMemcpyDeviceToHost, D.cs));
+        ZK_CUDA(cudaStreamSynchronize(D.cs));
+        ok = total_bad == 0;
+    }
+    D.p2p = ok;
+    D.p2p_tried = true;
+    u64 tab[MAX_WORLD] = {};
+    for (int g = 0; g < D.world; g++) tab[g] = (u64)(uintptr_t)D.peer_rows[g];
+    ZK_CUDA(cudaMemcpy(D.peer_tab, tab, sizeof(u64) * D.world, cudaMemcpyHostToDevice));
+    if (getenv("ZKGPU_DIST_TRACE")) fprintf(stderr, "[zkgpu dist] rank %d/%d: row shard %llu MiB, exchange = %s\n", D.rank, D.world,
+                                            (unsigned long long)(need_words >> 17), ok ? "peer stores (fused into the LDE)" : "ncclSend/ncclRecv");
+    return 0;
+}
+
+struct PieceSrc
+{
+    const u64 *p;
+    u64 ld;
+};
+
+__global__ void dist_unpack_kernel(u64 *dst, u64 dst_ld, const u64 *src, u64 nrows, u64 w)
+{
+    const u64 total = nrows * w;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (u64)gridDim.x * blockDim.x)
+    {
+        const u64 r = i / w, c = i - r * w;
+        dst[r * dst_ld + c] = src[i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// the program of one rank.  Runs with the rank's context locked and its device current.
+//   pieces[k]   : this rank's N x w(k, rank) piece of round k (device memory, or host memory which is staged)
+//   tree        : destination of the (2*NExt-1)*4 node words.  shared_host_tree: host memory every rank of this process
+//                 writes its own level slices into (single-process form).  gather (same value on every rank): the level
+//                 slices are shipped to rank 0, whose `tree` (device or host) receives the whole array; the other ranks
+//                 pass nullptr.  Neither: the tree stays sharded (subtrees per rank, top levels on rank 0).
+//   ext_host    : single-process form only: the caller's NExt x ncols host buffer; every rank copies out its rows
+// ---------------------------------------------------------------------------------------------------
+static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64 n_ext, u64 n, u64 ncols, u64 *tree,
+                            bool shared_host_tree, bool gather, u64 *ext_host)
+{
+    Dist &D = *C.dist;
+    const int G = D.world, me = D.rank;
+    unsigned log_n = 0, log_e = 0, lgR = 0;
+    while (((u64)1 << log_n) < n) log_n++;
+    while (((u64)1 << log_e) < n_ext) log_e++;
+    const unsigned log_b = log_e - log_n;
+    const u64 R = n_ext / (u64)G;
+    while (((u64)1 << lgR) < R) lgR++;
+    if (R == 0 || R * (u64)G != n_ext)
+    {
+        set_error("zkgpu dist: N_Extended = %llu must be a multiple of the number of GPUs (%d)", (unsigned long long)n_ext, G);
+        return -1;
+    }
+    Plan pl;
+    ZK_TRY(make_plan(pl, ncols, G, host_input));
+    cudaStream_t st = C.cur;
+    ZK_TRY(ctx_pipe_streams(C));
+    ZK_TRY(dist_setup_rows(C, D, R * ncols));
+    D.rows_n = R;
+    D.rows_c = ncols;
+    const u64 sub_words = (2 * R - 1) * 4;
+    ZK_TRY(dev_realloc(&D.sub, &D.sub_cap, sub_words));
+    u64 wmax = 0, rwmax = 0;
+    for (int k = 0; k < pl.rounds; k++)
+    {
+        if (pl.w[k][me] > wmax) wmax = pl.w[k][me];
+        if (pl.round_w[k] > rwmax) rwmax = pl.round_w[k];
+    }
+    ZK_TRY(ctx_ensure_scratch(C, 2 * n * (wmax ? wmax : 1)));
+    if (host_input) ZK_TRY(dev_realloc(&D.in_buf, &D.in_cap, 2 * n * wmax));
+    if (!D.p2p)
+    {
+        ZK_TRY(dev_realloc(&D.ext_buf, &D.ext_cap, 2 * n_ext * wmax));
+        ZK_TRY(dev_realloc(&D.recv_buf, &D.recv_cap, 2 * R * rwmax));
+    }
+    const bool tree_is_dev = tree != nullptr && is_device_ptr(tree);
+    u64 *tree_d = tree_is_dev ? tree : nullptr; // rank 0's device image of the whole tree, when there is one
+    if (me == 0 && gather && !tree_is_dev)
+    {
+        ZK_TRY(dev_realloc(&D.tree_dev, &D.tree_cap, (2 * n_ext - 1) * 4));
+        tree_d = D.tree_dev;
+    }
+
+    ctx_pipe_event(C, nullptr, st);
+    C.segs.clear();
+    ZK_CUDA(cudaEventRecord(C.ev[4], st));
+    // nobody may still be reading its rows (previous commit) when a peer starts storing into them
+    ZK_TRY(dist_barrier(D, st, st, D.ev_a, D.ev_b));
+
+    auto issue_h2d = [&](int k) -> int {
+        const int b = k & 1;
+        const u64 w = pl.w[k][me];
+        if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[b], 0));
+        if (w)
+            ZK_CUDA(cudaMemcpy2DAsync(D.in_buf + (size_t)b * n * wmax, w * sizeof(u64), pieces[k].p, pieces[k].ld * sizeof(u64), w * sizeof(u64), n,
+                                      cudaMemcpyHostToDevice, C.h2d));
+        ZK_CUDA(cudaEventRecord(C.in_ready[b], C.h2d));
+        return 0;
+    };
+    auto absorb_round = [&](int k) -> int {
+        ZK_CUDA(cudaStreamWaitEvent(st, D.ev_bar[k], 0));
+        if (!D.p2p)
+        {
+            const u64 *rb = D.recv_buf + (size_t)(k & 1) * R * rwmax;
+            for (int g = 0; g < G; g++)
+            {
+                const u64 w = pl.w[k][g];
+                if (w)
+                {
+                    u64 blocks = (R * w + 255) / 256;
+                    if (blocks > (u64)C.num_sms * 32) blocks = (u64)C.num_sms * 32;
+                    dist_unpack_kernel<<<(unsigned)blocks, 256, 0, st>>>(D.rows + pl.c0[k][g], ncols, rb, R, w);
+                    ZK_LAUNCHED();
+                    ZK_CUDA(cudaGetLastError());
+                }
+                rb += R * w;
+            }
+            ZK_CUDA(cudaEventRecord(D.ev_unp[k], st));
+        }
+        if (ext_host && pl.round_w[k])
+        {
+            // this round's columns of my rows are complete: send them home while the sponge runs
+            ZK_CUDA(cudaEventRecord(C.out_ready[0], st));
+            ZK_CUDA(cudaStreamWaitEvent(C.d2h, C.out_ready[0], 0));
+            ZK_CUDA(cudaMemcpy2DAsync(ext_host + (size_t)me * R * ncols + pl.round_c0[k], ncols * sizeof(u64), D.rows + pl.round_c0[k],
+                                      ncols * sizeof(u64), pl.round_w[k] * sizeof(u64), R, cudaMemcpyDeviceToHost, C.d2h));
+        }
+        if (ncols > 4 && pl.round_w[k])
+        {
+            int e0, e1;
+            ZK_TRY(ctx_pipe_event(C, &e0, st));
+            ZK_TRY(merkle_absorb(D.sub, D.rows + pl.round_c0[k], pl.round_w[k], ncols, R, k == 0, st));
+            ZK_TRY(ctx_pipe_event(C, &e1, st));
+            C.segs.push_back({1, e0, e1});
+        }
+        return 0;
+    };
+
+    if (host_input)
+    {
+        ZK_CUDA(cudaEventRecord(C.in_free[0], st));
+        ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[0], 0));
+        ZK_TRY(issue_h2d(0));
+    }
+    for (int k = 0; k < pl.rounds; k++)
+    {
+        const int b = k & 1;
+        const u64 w = pl.w[k][me];
+        const u64 *src = pieces[k].p;
+        u64 src_ld = pieces[k].ld;
+        if (host_input)
+        {
+            if (k + 1 < pl.rounds) ZK_TRY(issue_h2d(k + 1));
+            ZK_CUDA(cudaStreamWaitEvent(st, C.in_ready[b], 0));
+            src = D.in_buf + (size_t)b * n * wmax;
+            src_ld = w;
+        }
+        int e0, e1;
+        ZK_TRY(ctx_pipe_event(C, &e0, st));
+        u64 *ext = D.p2p ? nullptr : D.ext_buf + (size_t)b * n_ext * wmax;
+        if (w)
+        {
+            if (D.p2p)
+            {
+                Scatter sc;
+                sc.peer_tab = D.peer_tab;
+                sc.lg_rows = lgR;
+                sc.ld = ncols;
+                sc.col0 = pl.c0[k][me];
+                ZK_TRY(lde_strip(nullptr, 0, src, src_ld, C.scratch, log_n, log_b, w, st, &sc));
+            }
+            else
+                ZK_TRY(lde_strip(ext, w, src, src_ld, C.scratch, log_n, log_b, w, st));
+        }
+        ZK_TRY(ctx_pipe_event(C, &e1, st));
+        C.segs.push_back({0, e0, e1});
+        if (host_input) ZK_CUDA(cudaEventRecord(C.in_free[b], st));
+        // exchange point of round k
+        ZK_CUDA(cudaEventRecord(D.ev_lde[k], st));
+        ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_lde[k], 0));
+        if (D.p2p)
+            ZK_NCCL(g_nccl.AllReduce(D.flag, D.flag + 1, 1, ncclUint64, ncclSum, D.comm, D.cs)); // all stores of round k have landed
+        else
+        {
+            if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_unp[k - 2], 0)); // the receive slot has been unpacked
+            u64 *rb = D.recv_buf + (size_t)b * R * rwmax;
+            ZK_NCCL(g_nccl.GroupStart());
+            for (int g = 0; g < G; g++)
+            {
+                if (w) ZK_NCCL(g_nccl.Send(ext + (size_t)g * R * w, R * w, ncclUint64, g, D.comm, D.cs));
+                if (pl.w[k][g]) ZK_NCCL(g_nccl.Recv(rb, R * pl.w[k][g], ncclUint64, g, D.comm, D.cs));
+                rb += R * pl.w[k][g];
+            }
+            ZK_NCCL(g_nccl.GroupEnd());
+        }
+        ZK_CUDA(cudaEventRecord(D.ev_bar[k], D.cs));
+        if (k > 0) ZK_TRY(absorb_round(k - 1));
+    }
+    if (pl.rounds > 0) ZK_TRY(absorb_round(pl.rounds - 1));
+    if (ncols <= 4)
+    {
+        // rows of <= 4 words are copied, not hashed (poseidon_goldilocks.cpp:234-239)
+        int e0, e1;
+        ZK_TRY(ctx_pipe_event(C, &e0, st));
+        ZK_TRY(merkle_leaves(D.sub, D.rows, ncols, ncols, R, st));
+        ZK_TRY(ctx_pipe_event(C, &e1, st));
+        C.segs.push_back({1, e0, e1});
+    }
+    ZK_CUDA(cudaEventRecord(C.ev[2], st));
+    ZK_TRY(merkle_levels(D.sub, R, st));
+
+    // ---- stitch: level l of the global tree = the ranks' slices side by side (l <= log2 R), then the top over the sub-roots
+    u64 soff[40], scnt[40], goff[40], gcnt[40];
+    const int sl = subtree_levels(R, soff, scnt);
+    subtree_levels(n_ext, goff, gcnt);
+    const int LR = sl - 1; // level of the sub-roots
+    ZK_CUDA(cudaEventRecord(D.ev_a, st));
+    ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_a, 0));
+    u64 *top_dst = (me == 0 && tree_d) ? tree_d + goff[LR] : D.top;
+    ZK_NCCL(g_nccl.AllGather(D.sub + soff[LR], top_dst, 4, ncclUint64, D.comm, D.cs));
+    if (gather)
+    {
+        // process-per-GPU form, or a device tree on rank 0: every rank ships its level slices to rank 0
+        ZK_NCCL(g_nccl.GroupStart());
+        for (int l = 0; l < LR; l++)
+        {
+            if (me != 0)
+                ZK_NCCL(g_nccl.Send(D.sub + soff[l], scnt[l] * 4, ncclUint64, 0, D.comm, D.cs));
+            else
+                for (int g = 1; g < G; g++) ZK_NCCL(g_nccl.Recv(tree_d + goff[l] + (size_t)g * scnt[l] * 4, scnt[l] * 4, ncclUint64, g, D.comm, D.cs));
+        }
+        ZK_NCCL(g_nccl.GroupEnd());
+        if (me == 0)
+            for (int l = 0; l < LR; l++)
+                ZK_CUDA(cudaMemcpyAsync(tree_d + goff[l], D.sub + soff[l], scnt[l] * 32, cudaMemcpyDeviceToDevice, st));
+    }
+    ZK_CUDA(cudaEventRecord(D.ev_b, D.cs));
+    ZK_CUDA(cudaStreamWaitEvent(st, D.ev_b, 0));
+    if (me == 0) ZK_TRY(merkle_levels(top_dst, (u64)G, st));
+    ZK_CUDA(cudaEventRecord(C.ev[3], st));
+    C.timed = true;
+    if (shared_host_tree && tree)
+    {
+        for (int l = 0; l < LR; l++)
+            ZK_CUDA(cudaMemcpyAsync(tree + goff[l] + (size_t)me * scnt[l] * 4, D.sub + soff[l], scnt[l] * 32, cudaMemcpyDeviceToHost, st));
+        if (me == 0) ZK_CUDA(cudaMemcpyAsync(tree + goff[LR], top_dst, (2 * (size_t)G - 1) * 32, cudaMemcpyDeviceToHost, st));
+    }
+    else if (me == 0 && tree && !tree_is_dev)
+        ZK_CUDA(cudaMemcpyAsync(tree, tree_d, (2 * n_ext - 1) * 32, cudaMemcpyDeviceToHost, st));
+    if (ext_host)
+    {
+        ZK_CUDA(cudaEventRecord(C.out_free[0], C.d2h));
+        ZK_CUDA(cudaStreamWaitEvent(st, C.out_free[0], 0));
+    }
+    ZK_CUDA(cudaEventRecord(C.ev[5], st));
+    if (host_input || ext_host || (tree && !tree_is_dev))
+    {
+        ZK_CUDA(cudaStreamSynchronize(st));
+        ZK_CUDA(cudaEventElapsedTime(&C.stage[4], C.ev[4], C.ev[5]));
+    }
+    return 0;
+}
+
+// the single-process form: one worker thread per device, each running the rank program on its own context
+int dist_world_of_process() { return g_group.n; }
+
+int dist_multi_commit(u64 *out_ext, u64 *tree, const u64 *input, u64 n_ext, u64 n, u64 ncols)
+{
+    const int G = g_group.n;
+    if (is_device_ptr(input) || (out_ext && is_device_ptr(out_ext)))
+    {
+        set_error("zkgpu multi-GPU commit: the trace and the extended trace must be host buffers (or out_ext NULL: the extended "
+                  "trace stays on the devices as row shards); the tree may be a host buffer or memory of device 0");
+        return -1;
+    }
+    const bool tree_dev = tree && is_device_ptr(tree);
+    Plan pl;
+    ZK_TRY(make_plan(pl, ncols, G, true));
+    int rcs[MAX_WORLD] = {};
+    char errs[MAX_WORLD][512];
+    std::vector<std::thread> th;
+    for (int g = 0; g < G; g++)
+        th.emplace_back([&, g]() {
+            Enter en(g_group.ctx[g]->device);
+            if (en.rc < 0)
+            {
+                rcs[g] = en.rc;
+                snprintf(errs[g], sizeof(errs[g]), "%s", last_error());
+                // a rank that cannot even enter would leave the others waiting at the first barrier: nothing sane to do
+                // but report; contexts were created in zkgpu_init_multi, so this does not happen in practice
+                return;
+            }
+            PieceSrc ps[MAX_ROUNDS];
+            for (int k = 0; k < pl.rounds; k++) ps[k] = {input + pl.c0[k][g], ncols};
+            rcs[g] = dist_commit_rank(*en.c, ps, true, n_ext, n, ncols, (tree_dev && g != 0) ? nullptr : tree, tree && !tree_dev, tree_dev, out_ext);
+            if (rcs[g] < 0) snprintf(errs[g], sizeof(errs[g]), "%s", last_error());
+        });
+    for (auto &t : th) t.join();
+    for (int g = 0; g < G; g++)
+        if (rcs[g] < 0)
+        {
+            set_error("rank %d: %s", g, errs[g]);
+            return rcs[g];
+        }
+    return 0;
+}
+
+} // namespace zk
+
+using namespace zk;
+extern "C" {
+
+int zkgpu_nccl_unique_id(void *out128)
+{
+    ZK_TRY(nccl_load());
+    ncclUniqueId id;
+    ZK_NCCL(g_nccl.GetUniqueId(&id));
+    memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+int zkgpu_dist_init(const void *nccl_unique_id, int rank, int world)
+{
+    if (world < 1 || world > MAX_WORLD || (world & (world - 1)) || rank < 0 || rank >= world || !nccl_unique_id)
+    {
+        set_error("zkgpu_dist_init: need a unique id, 0 <= rank < world, world a power of two <= %d", MAX_WORLD);
+        return -1;
+    }
+    ZK_ENTER;
+    if (C.dist)
+    {
+        set_error("zkgpu_dist_init: this device already belongs to a job");
+        return -1;
+    }
+    ZK_TRY(nccl_load());
+    ncclUniqueId id;
+    memcpy(&id, nccl_unique_id, sizeof(id));
+    ncclComm_t comm = nullptr;
+    ZK_NCCL(g_nccl.CommInitRank(&comm, world, id, rank));
+    return dist_create(C, rank, world, comm, false);
+}
+
+int zkgpu_init_multi(int ngpu)
+{
+    int have = zkgpu_device_count();
+    if (ngpu <= 0) ngpu = have;
+    if (ngpu > have || ngpu > MAX_WORLD || (ngpu & (ngpu - 1)) || ngpu < 1)
+    {
+        set_error("zkgpu_init_multi: %d GPUs requested, %d visible; need a power of two <= %d", ngpu, have, MAX_WORLD);
+        return -1;
+    }
+    if (g_group.n)
+    {
+        if (g_group.n == ngpu) return 0;
+        set_error("zkgpu_init_multi: already initialised with %d GPUs", g_group.n);
+        return -1;
+    }
+    if (ngpu == 1) return zkgpu_init(0);
+    ZK_TRY(nccl_load());
+    int devs[MAX_WORLD];
+    for (int g = 0; g < ngpu; g++)
+    {
+        devs[g] = g;
+        Enter en(g);
+        if (en.rc < 0) return en.rc;
+        g_group.ctx[g] = en.c;
+        for (int h = 0; h < ngpu; h++)
+            if (h != g)
+            {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, g, h) == cudaSuccess && can)
+                {
+                    cudaError_t e = cudaDeviceEnablePeerAccess(h, 0);
+                    if (e != cudaSuccess) cudaGetLastError(); // already enabled is fine
+                }
+            }
+    }
+    ncclComm_t comms[MAX_WORLD];
+    ZK_NCCL(g_nccl.CommInitAll(comms, ngpu, devs));
+    for (int g = 0; g < ngpu; g++)
+    {
+        Enter en(g);
+        if (en.rc < 0) return en.rc;
+        ZK_TRY(dist_create(*en.c, g, ngpu, comms[g], true));
+    }
+    g_group.n = ngpu;
+    zk::Enter back(0); // the calling thread stays bound to device 0
+    return back.rc;
+}
+
+int zkgpu_dist_info(int *rank, int *world, int *peer_stores)
+{
+    ZK_ENTER;
+    if (rank) *rank = C.dist ? C.dist->rank : 0;
+    if (world) *world = g_group.n ? g_group.n : (C.dist ? C.dist->world : 1);
+    if (peer_stores) *peer_stores = C.dist ? (C.dist->p2p ? 1 : 0) : 0;
+    return 0;
+}
+
+int zkgpu_dist_plan(uint64_t ncols, int world, int host_input, int *rounds, uint64_t *c0, uint64_t *w)
+{
+    if (world < 1 || world > MAX_WORLD)
+    {
+        set_error("zkgpu_dist_plan: world out of range");
+        return -1;
+    }
+    Plan pl;
+    ZK_TRY(make_plan(pl, ncols, world, host_input != 0));
+    if (rounds) *rounds = pl.rounds;
+    for (int k = 0; k < pl.rounds; k++)
+        for (int g = 0; g < world; g++)
+        {
+            if (c0) c0[k * world + g] = pl.c0[k][g];
+            if (w) w[k * world + g] = pl.w[k][g];
+        }
+    return 0;
+}
+
+int zkgpu_dist_commit(void *, uint64_t *tree, const uint64_t *const *pieces, const uint64_t *piece_ld, int host_input, int gather_tree,
+                      uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    if (n == 0 || n_ext == 0) return 0;
+    if ((n & (n - 1)) || (n_ext & (n_ext - 1)) || n_ext < n)
+    {
+        set_error("dist_commit: N and N_Extended must be powers of two with N_Extended >= N");
+        return -1;
+    }
+    ZK_ENTER;
+    if (!C.dist || C.dist->single_process)
+    {
+        set_error("dist_commit: call zkgpu_dist_init first (process-per-GPU form); after zkgpu_init_multi use zkgpu_extend_and_merkelize");
+        return -1;
+    }
+    Plan pl;
+    ZK_TRY(make_plan(pl, ncols, C.dist->world, host_input != 0));
+    PieceSrc ps[MAX_ROUNDS];
+    for (int k = 0; k < pl.rounds; k++)
+    {
+        ps[k] = {pieces[k], piece_ld[k]};
+        if (pl.w[k][C.dist->rank] && (pieces[k] == nullptr || is_device_ptr(pieces[k]) == (host_input != 0)))
+        {
+            set_error("dist_commit: piece %d must be a %s pointer", k, host_input ? "host" : "device");
+            return -1;
+        }
+    }
+    return dist_commit_rank(C, ps, host_input != 0, n_ext, n, ncols, tree, false, gather_tree != 0, nullptr);
+}
+
+int zkgpu_dist_rows(uint64_t **rows, uint64_t *nrows, uint64_t *ncols, uint64_t **subtree)
+{
+    ZK_ENTER;
+    if (!C.dist)
+    {
+        set_error("dist_rows: no multi-GPU job on this device");
+        return -1;
+    }
+    if (rows) *rows = C.dist->rows;
+    if (nrows) *nrows = C.dist->rows_n;
+    if (ncols) *ncols = C.dist->rows_c;
+    if (subtree) *subtree = C.dist->sub;
+    return 0;
+}
+
+} // extern "C"

@@ -32,10 +32,6 @@
 #include "gl64.cuh"
 #include "zk_internal.h"
 #include <cstdlib>
-#include <map>
-#include <mutex>
-#include <tuple>
-#include <vector>
 
 namespace zk {
 
@@ -63,6 +59,10 @@ struct PassParams
     int post_mode;
     u64 post_const;
     const u64 *H0, *H1;
+    // last pass only, sharded commit: scatter over the peers' row shards (zk_internal.h: Scatter)
+    const u64 *peer_tab;
+    u32 sc_lg_b, sc_coset, sc_lg_rows;
+    u64 sc_col0;
 };
 
 __device__ u64 g_w256[256]; // w_256^i, Goldilocks::W[8]^i (goldilocks_base_field.cpp:11-44)
@@ -288,6 +288,13 @@ __global__ void __launch_bounds__(PassCfg<LR1, LR2>::THREADS) ntt_pass_kernel(co
             drow = (o << (P.lgNp + P.lgM)) + ((u64)kp << P.lgM) + rp;
             v = gl::canon(v);
         }
+        if (P.peer_tab)
+        {
+            const u64 e = (drow << P.sc_lg_b) + P.sc_coset;
+            u64 *base = reinterpret_cast<u64 *>(__ldg(P.peer_tab + (e >> P.sc_lg_rows)));
+            base[(e & (((u64)1 << P.sc_lg_rows) - 1)) * P.dst_ld + P.sc_col0 + c] = v;
+            return;
+        }
         P.dst[drow * P.dst_ld + c] = v;
     };
 
@@ -339,17 +346,26 @@ __global__ void build_pow_tables(u64 *G0, u64 *G1, u64 g, u64 scale, u32 n1)
     if (i < n1) G1[i] = gl::mul(scale, dev_pow(g, (u64)i << 12));
 }
 
-static std::mutex g_tab_mu;
-static std::map<std::tuple<u64, u64, unsigned>, std::pair<u64 *, u64 *>> g_tabs;
-static bool g_w256_ready = false;
-
+// Tables live in the calling thread's context (one set per device).  The build kernel is enqueued on the caller's stream;
+// an event recorded after every build is waited on by every later user, so a table built on one stream is safe to read
+// from another (zkgpu_set_stream).  The cache is bounded: past 96 entries (a blowup-16 LDE needs 18) it is flushed.
 int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64 **G1, cudaStream_t st)
 {
-    std::lock_guard<std::mutex> lk(g_tab_mu);
+    Ctx &C = *t_ctx;
     auto key = std::make_tuple(g, scale, log_n);
-    auto it = g_tabs.find(key);
-    if (it == g_tabs.end())
+    auto it = C.tabs.find(key);
+    if (it == C.tabs.end())
     {
+        if (C.tabs.size() >= 96)
+        {
+            ZK_CUDA(cudaDeviceSynchronize());
+            for (auto &kv : C.tabs)
+            {
+                cudaFree(kv.second.first);
+                cudaFree(kv.second.second);
+            }
+            C.tabs.clear();
+        }
         const u32 n1 = log_n > 12 ? (1u << (log_n - 12)) : 1u;
         u64 *d0 = nullptr, *d1 = nullptr;
         ZK_CUDA(cudaMalloc(&d0, 4096 * sizeof(u64)));
@@ -358,8 +374,11 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
         build_pow_tables<<<(n + 255) / 256, 256, 0, st>>>(d0, d1, g, scale, n1);
         ZK_LAUNCHED();
         ZK_CUDA(cudaGetLastError());
-        it = g_tabs.emplace(key, std::make_pair(d0, d1)).first;
+        ZK_CUDA(cudaEventRecord(C.tab_ev, st));
+        it = C.tabs.emplace(key, std::make_pair(d0, d1)).first;
     }
+    else
+        ZK_CUDA(cudaStreamWaitEvent(st, C.tab_ev, 0));
     *G0 = it->second.first;
     *G1 = it->second.second;
     return 0;
@@ -367,15 +386,14 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
 
 static int ensure_w256(cudaStream_t st)
 {
-    std::lock_guard<std::mutex> lk(g_tab_mu);
-    if (g_w256_ready) return 0;
+    Ctx &C = *t_ctx;
+    if (C.w256_ready) return 0;
     u64 h[256];
     const u64 w = gl::root_of_unity(8);
     h[0] = 1;
     for (int i = 1; i < 256; i++) h[i] = gl::mul_slow(h[i - 1], w);
-    ZK_CUDA(cudaMemcpyToSymbolAsync(g_w256, h, sizeof(h), 0, cudaMemcpyHostToDevice, st));
-    ZK_CUDA(cudaStreamSynchronize(st));
-    g_w256_ready = true;
+    ZK_CUDA(cudaMemcpyToSymbol(g_w256, h, sizeof(h))); // synchronous: every later stream sees it
+    C.w256_ready = true;
     return 0;
 }
 
@@ -402,39 +420,43 @@ static int launch_pass(const PassParams &P, bool inv, cudaStream_t st)
     return 0;
 }
 
-static int g_num_sms = 0;
-int g_ntt_force_v1 = 0;
-int g_ntt_threads_per_sm_cap = 0; // 0: fill the SM // test hook (ZKGPU_NTT_V1=1): always use the simple per-tile kernel
+int g_ntt_force_v1 = 0;           // test hook (ZKGPU_NTT_V1=1): always use the simple per-tile kernel
+int g_ntt_threads_per_sm_cap = 0; // 0: fill the SM
+
+// resident CTAs per SM of a kernel on the current device (also raises its dynamic shared-memory limit there, once)
+template <typename K>
+static int kernel_occupancy(K kern, int threads, size_t smem, int *out)
+{
+    Ctx &C = *t_ctx;
+    auto it = C.occupancy.find((const void *)kern);
+    if (it == C.occupancy.end())
+    {
+        if (smem > 48 * 1024) ZK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int nb = 0;
+        ZK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, threads, smem));
+        if (nb < 1) nb = 1;
+        it = C.occupancy.emplace((const void *)kern, nb).first;
+    }
+    *out = it->second;
+    return 0;
+}
 
 template <int LR1, int LR2>
 static int launch_tile(const PassParams &P, bool inv, cudaStream_t st)
 {
     using Cfg = TileCfg<LR1, LR2>;
-    static int blocks_per_sm[2] = {0, 0};
     auto kf = ntt_tile_kernel<LR1, LR2, false>;
     auto ki = ntt_tile_kernel<LR1, LR2, true>;
-    if (!blocks_per_sm[inv])
-    {
-        if (!g_num_sms)
-        {
-            int dev = 0;
-            ZK_CUDA(cudaGetDevice(&dev));
-            ZK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-        }
-        ZK_CUDA(cudaFuncSetAttribute(inv ? ki : kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-        int nb = 0;
-        ZK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, inv ? ki : kf, Cfg::THREADS, Cfg::SMEM));
-        if (nb < 1) nb = 1;
-        blocks_per_sm[inv] = nb;
-    }
+    int bps = 1;
+    ZK_TRY(kernel_occupancy(inv ? ki : kf, Cfg::THREADS, Cfg::SMEM, &bps));
     const u64 ntiles = (P.totalQ + 15) / 16;
-    u64 grid = (u64)g_num_sms * blocks_per_sm[inv];
+    u64 grid = (u64)t_ctx->num_sms * bps;
     // experiment knob (zkgpu_tune key 1): leave most of each SM to another kernel
     if (g_ntt_threads_per_sm_cap > 0)
     {
         u64 b = (u64)g_ntt_threads_per_sm_cap / Cfg::THREADS;
         if (b < 1) b = 1;
-        if (b < (u64)blocks_per_sm[inv]) grid = (u64)g_num_sms * b;
+        if (b < (u64)bps) grid = (u64)t_ctx->num_sms * b;
     }
     if (grid > ntiles) grid = ntiles;
     if (grid == 0) return 0;
@@ -479,7 +501,7 @@ static int dispatch_pass(const PassParams &P, bool inv, cudaStream_t st)
 }
 
 int ntt_transform(u64 *dst, u64 dst_ld, const u64 *src, u64 src_ld, u64 *tmp, unsigned L, u64 ncols, bool inverse,
-                  const Scale &pre, const Scale &post, cudaStream_t st)
+                  const Scale &pre, const Scale &post, cudaStream_t st, const Scatter *sc, unsigned sc_log_b, unsigned sc_coset)
 {
     if (ncols == 0) return 0;
     if (L > 30)
@@ -536,6 +558,16 @@ int ntt_transform(u64 *dst, u64 dst_ld, const u64 *src, u64 src_ld, u64 *tmp, un
         P.H0 = post.G0;
         P.H1 = post.G1;
         P.totalQ = ((u64)1 << (L - lg[p])) * ncols;
+        if (sc && last)
+        {
+            P.peer_tab = sc->peer_tab;
+            P.sc_lg_b = sc_log_b;
+            P.sc_coset = sc_coset;
+            P.sc_lg_rows = sc->lg_rows;
+            P.sc_col0 = sc->col0;
+            P.dst = nullptr;
+            P.dst_ld = sc->ld;
+        }
         ZK_TRY(dispatch_pass(P, inverse, st));
         consumed += lg[p];
     }
@@ -543,7 +575,7 @@ int ntt_transform(u64 *dst, u64 dst_ld, const u64 *src, u64 src_ld, u64 *tmp, un
 }
 
 int lde_strip(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, u64 *scratch, unsigned log_n, unsigned log_blowup,
-              u64 ncols, cudaStream_t st)
+              u64 ncols, cudaStream_t st, const Scatter *sc)
 {
     if (ncols == 0) return 0;
     const u64 n = (u64)1 << log_n;
@@ -561,7 +593,10 @@ int lde_strip(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, u64 *scratch, unsi
         Scale pre;
         pre.mode = SCALE_POWER;
         ZK_TRY(get_power_tables(g, ninv, log_n, &pre.G0, &pre.G1, st));
-        ZK_TRY(ntt_transform(out + r * out_ld, out_ld * b, coef, ncols, tmp, log_n, ncols, false, pre, none, st));
+        if (sc)
+            ZK_TRY(ntt_transform(nullptr, 0, coef, ncols, tmp, log_n, ncols, false, pre, none, st, sc, log_blowup, (unsigned)r));
+        else
+            ZK_TRY(ntt_transform(out + r * out_ld, out_ld * b, coef, ncols, tmp, log_n, ncols, false, pre, none, st));
         g = gl::mul_slow(g, wext);
     }
     return 0;

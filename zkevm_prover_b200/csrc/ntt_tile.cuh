@@ -41,6 +41,10 @@ struct StepOut
     u64 post_const;
     const u64 *H0, *H1;
     bool canon;    // canonicalise before the global store (last pass)
+    // sharded commit (last pass of a coset transform): scatter over the peers' row shards, see zk_internal.h: Scatter
+    const u64 *peer_tab;
+    u32 sc_lg_b, sc_coset, sc_lg_rows;
+    u64 sc_col; // sc_col0 + column of this lane
 };
 
 // E = 2^LOGE words at buf[(base + j*stride) * 16], j < E, each multiplied by tw[twbase + j*twstride] (if tw != nullptr),
@@ -73,11 +77,28 @@ __device__ __noinline__ void tile_step(u64 *buf, int base, int stride, const u64
         for (int j = 0; j < E; j++) a[j] = j < E / 2 ? buf[(base + j * stride) * 16] : gl::canon(buf[(base + j * stride) * 16]);
     }
     dft_regs<LOGE, INV, true>(a); // the first butterfly stage skips its own canon()
-    const bool scaled = out.dst != nullptr && out.post_mode != SCALE_NONE;
+    const bool scatter = out.peer_tab != nullptr;
+    const bool scaled = !scatter && out.dst != nullptr && out.post_mode != SCALE_NONE;
     if (out.dst == nullptr || scaled)
     {
 #pragma unroll
         for (int k = 0; k < E; k++) buf[(base + k * stride) * 16] = a[k];
+        if (scatter)
+        {
+            // rolled like the post-scaled path: the destination GPU changes with the top bits of the output row
+            u64 row = out.row0;
+            const u64 mask = ((u64)1 << out.sc_lg_rows) - 1;
+#pragma unroll 1
+            for (int k = 0; k < E; k++)
+            {
+                const u64 v = gl::canon(buf[(base + k * stride) * 16]);
+                const u64 e = (row << out.sc_lg_b) + out.sc_coset;
+                u64 *pb = reinterpret_cast<u64 *>(__ldg(out.peer_tab + (e >> out.sc_lg_rows)));
+                pb[(e & mask) * out.dst_ld + out.sc_col] = v;
+                row += out.row_step;
+            }
+            return;
+        }
         if (!scaled) return;
         // Post-scaled output (INTT's 1/N or 7^i/N: zkgpu_ntt only, never the LDE): a rolled loop over the values just
         // parked in shared memory.  Keeping the three output flavours inside the unrolled store loop tripled the code
@@ -268,7 +289,12 @@ __global__ void __launch_bounds__(TileCfg<LR1, LR2>::THREADS, 512 / TileCfg<LR1,
         if (cur.active)
         {
             StepOut so;
-            so.dst = P.dst + cur.c;
+            so.peer_tab = P.is_last ? P.peer_tab : nullptr;
+            so.sc_lg_b = P.sc_lg_b;
+            so.sc_coset = P.sc_coset;
+            so.sc_lg_rows = P.sc_lg_rows;
+            so.sc_col = P.sc_col0 + cur.c;
+            so.dst = so.peer_tab ? nullptr : P.dst + cur.c;
             so.dst_ld = P.dst_ld;
             so.post_mode = P.is_last ? P.post_mode : SCALE_NONE;
             so.post_const = P.post_const;

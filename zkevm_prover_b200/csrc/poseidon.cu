@@ -710,10 +710,10 @@ __global__ void __launch_bounds__(128) level_kernel(u64 *parents, const u64 *chi
 // ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
-static bool g_consts_ready = false;
 int poseidon_init_constants()
 {
-    if (g_consts_ready) return 0;
+    Ctx &C = *t_ctx; // once per device: __constant__ arrays exist per device
+    if (C.consts_ready) return 0;
     ZK_CUDA(cudaMemcpyToSymbol(c_C, PG_C, sizeof(u64) * 118));
     {
         u64 pt[144], rc[96];
@@ -742,7 +742,7 @@ int poseidon_init_constants()
                 return -1;
             }
         }
-    g_consts_ready = true;
+    C.consts_ready = true;
     return 0;
 }
 
