@@ -110,6 +110,22 @@ int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *n
 int zkgpu_extend_and_merkelize(void *ntt, uint64_t *out_ext, uint64_t *tree, const uint64_t *input, uint64_t n_extended,
                                uint64_t n, uint64_t ncols);
 
+/* The commit cache (csrc/api.cu: Resident).  Unchanged starks.cpp calls ntt.extendPol(p_cm_2ns, ...) (starks.cpp:53) and then
+ * treesGL[k]->merkelize() on the same host buffer (starks.hpp:186).  zkgpu_extend_pol with host pointers therefore also
+ * hashes the strips while they are on the device and remembers the finished tree under (output pointer, rows, columns); the
+ * zkgpu_merkletree call on that buffer returns it without uploading the extended trace again.  A fingerprint of a few rows
+ * guards against a buffer that was modified in between; zkgpu_invalidate(ptr) (NULL = everything) drops entries explicitly;
+ * ZKGPU_FUSE_COMMIT=0 or zkgpu_tune(2, 0) turns the behaviour off. */
+int zkgpu_invalidate(const void *host_ptr);
+
+/* ---- stage 4 of Starks::genProof on the device (src/starkpil/starks.cpp:261-293):
+ *   nttExtended.INTT(qq1, q_2ns, NExt, qDim);  qq2[k*qDeg + p] = qq1[p*N + k] * shiftIn^p (shiftIn = (1/7)^N, :266-281);
+ *   nttExtended.NTT(cm4_2ns, qq2, NExt, qDim*qDeg);  treesGL[3]->merkelize().
+ * q_2ns: NExt x qDim, cm4_2ns: NExt x (qDim*qDeg), both host or both device pointers; tree: (2*NExt-1)*4 words, host or
+ * device, or NULL (no tree).  qDeg must not exceed NExt / N. */
+int zkgpu_stage4_commit(void *ntt_extended, uint64_t *cm4_2ns, uint64_t *tree, const uint64_t *q_2ns, uint64_t n_extended, uint64_t n,
+                        uint64_t q_dim, uint64_t q_deg);
+
 /* ---- constant-tree builder: the Goldilocks branch of buildConstTree (tools/starkpil/bctree/build_const_tree.cpp:533-596;
  * interpolate :398-531 is the same LDE as extendPol: 1/N * shift^i pre-scale :361-395, coset shift 7).
  * image receives the reference's on-disk layout  [nPols, nExt, extended constant polynomials (nExt x nPols, row-major),

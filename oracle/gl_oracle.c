@@ -17,6 +17,9 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include "poseidon_constants.h"
 
 typedef uint64_t u64;
@@ -182,6 +185,30 @@ void oracle_extend_pol(u64 *out, const u64 *in, u64 n_ext, u64 n, u64 ncols)
     free(coef);
 }
 
+
+/* Stage 4 of Starks::genProof (src/starkpil/starks.cpp:261-285):
+ *   nttExtended.INTT(qq1, q_2ns, NExt, qDim);
+ *   qq2[k*qDeg + p] = qq1[p*N + k] * shiftIn^p, shiftIn = (1/7)^N, every word of the qDim-word element (:264-281,
+ *   Goldilocks3::mul(Element&, Element&, Goldilocks::Element&), goldilocks_cubic_extension.hpp:1887-1892);
+ *   qq2 is zero beyond element N*qDeg (:233, calloc'ed Polinomial);  nttExtended.NTT(cm4_2ns, qq2, NExt, qDim*qDeg). */
+void oracle_stage4(u64 *cm4_2ns, const u64 *q_2ns, u64 n_ext, u64 n, u64 q_dim, u64 q_deg)
+{
+    u64 w = q_dim * q_deg;
+    u64 *qq1 = (u64 *)malloc(n_ext * q_dim * sizeof(u64));
+    u64 *qq2 = (u64 *)calloc(n_ext * w, sizeof(u64));
+    oracle_intt(qq1, q_2ns, n_ext, q_dim, 0);
+    u64 shift_in = gl_pow(gl_inv(7), n), cur = 1;
+    for (u64 p = 0; p < q_deg; p++)
+    {
+        for (u64 k = 0; k < n; k++)
+            for (u64 d = 0; d < q_dim; d++) qq2[(k * q_deg + p) * q_dim + d] = gl_mul(qq1[(p * n + k) * q_dim + d], cur);
+        cur = gl_mul(cur, shift_in);
+    }
+    ntt_forward(cm4_2ns, qq2, n_ext, w, n_ext);
+    free(qq1);
+    free(qq2);
+}
+
 /* ---------------- Poseidon (poseidon_goldilocks.cpp:5-37, hash_full_result_seq) ---------------- */
 static inline u64 pow7(u64 x)
 { /* poseidon_goldilocks.hpp:91-97 */
@@ -314,6 +341,15 @@ static inline u64 splitmix64(u64 x)
     x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
     x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
     return x ^ (x >> 31);
+}
+void oracle_set_threads(int n)
+{
+#ifdef _OPENMP
+    omp_set_dynamic(0);
+    omp_set_num_threads(n > 0 ? n : 1);
+#else
+    (void)n;
+#endif
 }
 void oracle_fill(u64 *x, u64 n, u64 seed, u64 offset)
 {

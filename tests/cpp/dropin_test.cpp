@@ -102,13 +102,93 @@ static void gpu_part()
     EXPECT(memcmp(x.data(), y.data(), M * 24) == 0);
 }
 
+static uint64_t splitmix(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+// The call pair of UNCHANGED starks.cpp (:53-57, starks.hpp:186): ntt.extendPol(cm_2ns, cm_n, NExt, N, nCols, buffer) and
+// then MerkleTreeGL(NExt, nCols, cm_2ns).merkelize() on the same host buffer.  The tree must equal the one computed from a
+// COPY of the extended trace (a different pointer: no commit-cache hit, the plain upload-and-hash path), the second
+// merkelize on the same buffer (entry consumed) must still be right, and a buffer modified in between must not get the
+// stale tree.
+static void commit_pair(uint64_t N, uint64_t NE, uint64_t C)
+{
+    std::vector<Goldilocks::Element> in(N * C), ext(NE * C), buf(NE * C);
+    for (uint64_t i = 0; i < N * C; i++) in[i].fe = splitmix(0x9E3779B97F4A7C15ULL + i) % GOLDILOCKS_PRIME;
+    NTT_Goldilocks ntt(N);
+    ntt.extendPol(ext.data(), in.data(), NE, N, C, buf.data());
+    MerkleTreeGL mt(NE, C, ext.data());
+    mt.merkelize(); // served by the commit cache
+    std::vector<Goldilocks::Element> copy(ext);
+    MerkleTreeGL ref(NE, C, copy.data());
+    ref.merkelize(); // uploaded and hashed
+    EXPECT(memcmp(mt.nodes, ref.nodes, mt.getTreeNumElements() * 8) == 0);
+    memset(mt.nodes, 0, mt.getTreeNumElements() * 8);
+    mt.merkelize(); // entry already consumed: plain path
+    EXPECT(memcmp(mt.nodes, ref.nodes, mt.getTreeNumElements() * 8) == 0);
+    // modified between the two calls: the fingerprint (or an explicit zkgpu_invalidate) must keep the stale tree away
+    ntt.extendPol(ext.data(), in.data(), NE, N, C, buf.data());
+    ext[0].fe ^= 1;
+    copy = ext;
+    mt.merkelize();
+    ref.merkelize();
+    EXPECT(memcmp(mt.nodes, ref.nodes, mt.getTreeNumElements() * 8) == 0);
+    ntt.extendPol(ext.data(), in.data(), NE, N, C, buf.data());
+    ext[(NE / 2 + 3) * C + 1].fe ^= 1; // not a fingerprint row: the caller must say so
+    zkgpu_invalidate(ext.data());
+    copy = ext;
+    mt.merkelize();
+    ref.merkelize();
+    EXPECT(memcmp(mt.nodes, ref.nodes, mt.getTreeNumElements() * 8) == 0);
+}
+
+// `dropin_test gpu2`: one process, two GPUs (zkgpu_init_multi) behind the same classes; trees and extended traces must
+// equal the 1-GPU ones word for word.
+static void gpu2_part()
+{
+    const uint64_t N = 1 << 16, NE = 1 << 17, C = 665;
+    std::vector<Goldilocks::Element> in(N * C), ext1(NE * C), ext2(NE * C), buf(NE * C);
+    for (uint64_t i = 0; i < N * C; i++) in[i].fe = splitmix(0x9E3779B97F4A7C15ULL + i) % GOLDILOCKS_PRIME;
+    NTT_Goldilocks ntt(N);
+    MerkleTreeGL t1(NE, C, ext1.data()), t2(NE, C, ext2.data());
+    zkgpu_dropin::check(zkgpu_extend_and_merkelize(ntt.handle(), zkgpu_dropin::words(ext1.data()), zkgpu_dropin::words(t1.nodes),
+                                                   zkgpu_dropin::words(in.data()), NE, N, C), "1 gpu");
+    zkgpu_dropin::check(zkgpu_init_multi(2), "zkgpu_init_multi");
+    zkgpu_dropin::check(zkgpu_extend_and_merkelize(ntt.handle(), zkgpu_dropin::words(ext2.data()), zkgpu_dropin::words(t2.nodes),
+                                                   zkgpu_dropin::words(in.data()), NE, N, C), "2 gpus");
+    EXPECT(memcmp(ext1.data(), ext2.data(), NE * C * 8) == 0);
+    EXPECT(memcmp(t1.nodes, t2.nodes, t1.getTreeNumElements() * 8) == 0);
+    // and the unchanged call pair, now served by both GPUs
+    memset(ext2.data(), 0, NE * C * 8);
+    memset(t2.nodes, 0, t2.getTreeNumElements() * 8);
+    ntt.extendPol(ext2.data(), in.data(), NE, N, C, buf.data());
+    t2.merkelize();
+    EXPECT(memcmp(ext1.data(), ext2.data(), NE * C * 8) == 0);
+    EXPECT(memcmp(t1.nodes, t2.nodes, t1.getTreeNumElements() * 8) == 0);
+    int rank = -1, world = 0, peer = -1;
+    zkgpu_dist_info(&rank, &world, &peer);
+    printf("gpu2: world %d, peer stores %d\n", world, peer);
+    EXPECT(world == 2);
+}
+
 int main(int argc, char **argv)
 {
     const bool gpu = argc > 1 && strcmp(argv[1], "gpu") == 0;
+    const bool gpu2 = argc > 1 && strcmp(argv[1], "gpu2") == 0;
     try
     {
         cpu_part();
-        if (gpu) gpu_part();
+        if (gpu)
+        {
+            gpu_part();
+            commit_pair(1 << 12, 1 << 13, 45);
+            commit_pair(1 << 14, 1 << 15, 665);
+        }
+        if (gpu2) gpu2_part();
     }
     catch (const std::exception &e)
     {

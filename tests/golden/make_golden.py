@@ -153,6 +153,19 @@ def diffs():
         L.zkref_canon(vp(o), u(o.size))
         out["cases"].append({"op": "fri_fold", "pol_bits": pol_bits, "next_bits": next_bits, "seed_offset": 4,
                              "shift_inv_and_x": "splitmix(seed+5)[3], splitmix(seed+5)[0:3]", "sha256": digest(o), "samples": samples(o)})
+    # stage 4 of Starks::genProof (starks.cpp:261-285) through the reference's NTT_Goldilocks + Goldilocks3::mul
+    # (oracle/ref_wrap.cpp zkref_stage4)
+    for (log_n, log_b, q_dim, q_deg) in [(10, 1, 3, 2), (8, 2, 3, 3), (12, 1, 3, 1), (6, 3, 3, 8), (16, 1, 3, 2)]:
+        n, n_ext = 1 << log_n, 1 << (log_n + log_b)
+        q = splitmix_fill(n_ext * q_dim, SEED + 6)
+        o = np.zeros(n_ext * q_dim * q_deg, dtype=np.uint64)
+        L.zkref_stage4(vp(o), vp(q.copy()), u(n_ext), u(n), u(q_dim), u(q_deg))
+        L.zkref_canon(vp(o), u(o.size))
+        tree = np.zeros((2 * n_ext - 1) * 4, dtype=np.uint64)
+        L.zkref_merkletree(vp(tree), vp(o), u(q_dim * q_deg), u(n_ext), u(1))
+        L.zkref_canon(vp(tree), u(tree.size))
+        out["cases"].append({"op": "stage4", "log_n": log_n, "log_blowup": log_b, "q_dim": q_dim, "q_deg": q_deg, "seed_offset": 6,
+                             "sha256": digest(o), "samples": samples(o), "root": ["%016x" % int(x) for x in tree[-4:]]})
     return out
 
 

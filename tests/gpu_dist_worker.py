@@ -1,0 +1,112 @@
+"""Worker processes of tests/test_gpu_dist.py (multi-GPU parity through the C ABI).  Not collected by pytest.
+
+  python gpu_dist_worker.py spawn WORLD LOG_N COLS LOG_B   process-per-GPU form (torch.distributed NCCL + zkgpu_dist_*)
+  python gpu_dist_worker.py multi WORLD LOG_N COLS LOG_B   single-process form (zkgpu_init_multi + zkgpu_extend_and_merkelize)
+Each compares every word of the tree and of every row shard with the 1-GPU result of the same library (which the
+other GPU tests pin to the oracle / compiled reference), plus the oracle itself when the shape is small."""
+import ctypes
+import os
+import pathlib
+import sys
+
+import numpy as np
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+SEED = 0x9E3779B97F4A7C15
+
+
+def single_gpu_result(zk, a, n, n_ext, c):
+    ext = np.zeros((n_ext, c), dtype=np.uint64)
+    tree = np.zeros((2 * n_ext - 1) * 4, dtype=np.uint64)
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n_ext, n, c)
+    return ext, tree
+
+
+def spawn_rank(rank, world, log_n, c, log_b, port, host_input, exchange):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    if exchange:
+        os.environ["ZKGPU_EXCHANGE"] = exchange
+    import torch
+    import torch.distributed as dist
+    import zkevm_prover_b200 as zk
+    from zkevm_prover_b200 import dist_commit as dc
+    from oracle_lib import Oracle
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+    try:
+        n, n_ext = 1 << log_n, 1 << (log_n + log_b)
+        a = Oracle().fill(n * c, SEED, 0).reshape(n, c)
+        zk.init(rank)
+        want_ext, want_tree = single_gpu_result(zk, a, n, n_ext, c)
+        cd = dc.CDist(dist, rank)
+        K, plan = cd.plan(c, host_input)
+        pieces = []
+        for k in range(K):
+            c0, w = plan[k][rank]
+            m = torch.from_numpy(np.ascontiguousarray(a[:, c0:c0 + w]).view(np.int64).reshape(-1).copy()) if w else torch.zeros(1, dtype=torch.int64)
+            pieces.append(m.pin_memory() if host_input else m.cuda())
+        R = n_ext // world
+        for rep in range(2):  # twice: the second call reuses the row shards (start-of-call barrier)
+            tree = torch.zeros((2 * n_ext - 1) * 4, dtype=torch.int64, device="cuda") if rank == 0 else None
+            cd.commit(pieces, n, n_ext, c, tree, host_input=host_input, gather=True)
+            zk.sync()
+            p, r, cc, sub = cd.rows()
+            assert (r, cc) == (R, c)
+            rows = np.zeros((R, c), dtype=np.uint64)
+            zk._check(zk.lib().zkgpu_memcpy(rows.ctypes.data, p, rows.nbytes))
+            assert np.array_equal(rows, want_ext[rank * R:(rank + 1) * R]), "rank %d: row shard differs (rep %d)" % (rank, rep)
+            if rank == 0:
+                got = tree.cpu().numpy().view(np.uint64)
+                bad = np.nonzero(got != want_tree)[0]
+                assert bad.size == 0, "tree differs at %d words, first %d (rep %d)" % (bad.size, bad[0], rep)
+        print("rank %d ok: peer_stores=%s rounds=%d" % (rank, cd.peer_stores(), K), flush=True)
+    finally:
+        dist.destroy_process_group()
+
+
+def main():
+    mode, world, log_n, c, log_b = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
+    extra = sys.argv[6] if len(sys.argv) > 6 else ""
+    if mode == "spawn":
+        import socket
+        import torch.multiprocessing as mp
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+        s.close()
+        mp.spawn(spawn_rank, args=(world, log_n, c, log_b, port, "host" in extra, "nccl" if "nccl" in extra else ""), nprocs=world, join=True)
+        print("dist spawn: ok")
+    elif mode == "multi":
+        if "nccl" in extra:
+            os.environ["ZKGPU_EXCHANGE"] = "nccl"
+        import torch  # before the library maps an NCCL: torch's own libnccl.so.2 must be the one this process holds
+        import zkevm_prover_b200 as zk
+        from oracle_lib import Oracle
+        n, n_ext = 1 << log_n, 1 << (log_n + log_b)
+        a = Oracle().fill(n * c, SEED, 0).reshape(n, c)
+        zk.init(0)
+        want_ext, want_tree = single_gpu_result(zk, a, n, n_ext, c)
+        zk._check(zk.lib().zkgpu_init_multi(world))
+        for rep in range(2):
+            ext = np.zeros((n_ext, c), dtype=np.uint64)
+            tree = np.zeros((2 * n_ext - 1) * 4, dtype=np.uint64)
+            zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n_ext, n, c)
+            assert np.array_equal(ext, want_ext), "extended trace differs (rep %d)" % rep
+            bad = np.nonzero(tree != want_tree)[0]
+            assert bad.size == 0, "tree differs at %d words, first %d (rep %d)" % (bad.size, bad[0] if bad.size else -1, rep)
+        # extended trace left on the devices, tree into memory of device 0
+        dtree = torch.zeros((2 * n_ext - 1) * 4, dtype=torch.int64, device="cuda:0")
+        zk.extend_and_merkelize(zk.NTT_Goldilocks(n), None, dtree, a, n_ext, n, c)
+        zk.sync()
+        assert np.array_equal(dtree.cpu().numpy().view(np.uint64), want_tree), "device-0 tree differs"
+        r, w, ps = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        zk._check(zk.lib().zkgpu_dist_info(ctypes.byref(r), ctypes.byref(w), ctypes.byref(ps)))
+        print("dist multi: ok world=%d peer_stores=%d" % (w.value, ps.value))
+    else:
+        raise SystemExit("unknown mode")
+
+
+if __name__ == "__main__":
+    main()

@@ -80,6 +80,13 @@ class Oracle:
         return self.canon(tree)
 
 
+    def stage4(self, q_2ns, n_ext, n, q_dim, q_deg):
+        """Starks::genProof stage 4 transforms (starks.cpp:261-285): q_2ns (NExt x qDim) -> cm4_2ns (NExt x qDim*qDeg)."""
+        q = np.ascontiguousarray(q_2ns, dtype=np.uint64).reshape(-1)
+        out = np.zeros((n_ext, q_dim * q_deg), dtype=np.uint64)
+        self.L.oracle_stage4(_vp(out), _vp(q), u64(n_ext), u64(n), u64(q_dim), u64(q_deg))
+        return self.canon(out)
+
     def fri_fold(self, fri_pol, pol_bits, next_bits, shift_inv, special_x):
         """One FRI folding step (friProve.cpp:89-106): fri_pol (2^pol_bits x 3) -> pol2_e (2^next_bits x 3)."""
         a = np.ascontiguousarray(fri_pol, dtype=np.uint64).reshape(-1)
@@ -145,6 +152,19 @@ class Reference:
         else:
             self.L.zkref_merkletree(_vp(tree), _vp(a), u64(ncols), u64(nrows), u64(dim))
         return self.canon(tree)
+
+    def reverse_permutation(self, src, size, offset_cols, ncols, ncols_all, extension=1):
+        src = np.ascontiguousarray(src, dtype=np.uint64).copy()
+        dst = np.zeros((size, ncols), dtype=np.uint64)
+        self.L.zkref_reverse_permutation(_vp(dst), _vp(src), u64(size), u64(offset_cols), u64(ncols), u64(ncols_all), int(extension))
+        return dst
+
+    def stage4(self, q_2ns, n_ext, n, q_dim, q_deg):
+        """Starks::genProof stage 4 (starks.cpp:261-285): q_2ns (NExt x qDim) -> cm4_2ns (NExt x qDim*qDeg)."""
+        q = np.ascontiguousarray(q_2ns, dtype=np.uint64).reshape(-1).copy()
+        out = np.zeros((n_ext, q_dim * q_deg), dtype=np.uint64)
+        self.L.zkref_stage4(_vp(out), _vp(q), u64(n_ext), u64(n), u64(q_dim), u64(q_deg))
+        return self.canon(out)
 
     def fri_fold(self, fri_pol, pol_bits, next_bits, shift_inv, special_x):
         a = np.ascontiguousarray(fri_pol, dtype=np.uint64).reshape(-1).copy()

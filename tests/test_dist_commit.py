@@ -42,7 +42,7 @@ class OracleOps:
 
     def absorb(self, leaves, block, block_off, width, ld, nrows, first, copy_to=None, copy_off=0, copy_ld=0):
         # running digest after a whole number of 8-word blocks == linear_hash of the row prefix absorbed so far
-        blk = self._np(block)[block_off: block_off + nrows * ld].reshape(nrows, ld)[:, :width]
+        blk = self._np(block)[block_off + np.arange(nrows)[:, None] * ld + np.arange(width)[None, :]]
         if copy_to is not None:
             self.copy_block(copy_to, copy_off, copy_ld, block, block_off, ld, nrows, width)
         self.prefix = blk.copy() if first else np.concatenate([self.prefix, blk], axis=1)
@@ -133,22 +133,26 @@ def test_commit_sharded_pipelined_gloo(world, n, b, c, rounds):
 
 
 def test_piece_plan():
+    """zkgpu_dist_plan (csrc/dist.cu make_plan; callable without a device): consecutive pieces covering the row, every
+    round but the last a whole number of sponge blocks, columns dealt out evenly."""
+    for world in (1, 2, 4, 8):
+        for host in (True, False):
+            K, plan = dc.piece_plan(665, world, None, host)
+            flat = [p for r in plan for p in r]
+            assert flat[0][0] == 0 and flat[-1][0] + flat[-1][1] == 665
+            assert all(a[0] + a[1] == b[0] for a, b in zip(flat[:-1], flat[1:]))
+            assert all(sum(w for _, w in r) % 8 == 0 for r in plan[:-1])
+            per_rank = [sum(plan[k][g][1] for k in range(K)) for g in range(world)]
+            assert max(per_rank) - min(per_rank) <= 1
+            if not host:
+                assert K == 1
+            else:
+                assert sum(w for _, w in plan[0]) == min(16 * world, 665) or K == 1
     K, plan = dc.piece_plan(665, 8)
-    assert K == 3 and plan[0][0] == (0, 16) and plan[1][0] == (128, 32) and plan[2][7] == (640, 25)
-    assert dc.piece_plan(665, 8, 3)[1][0][0] == (0, 32)  # explicit rounds: equal rounds
-    flat = [p for r in plan for p in r]
-    assert all(a[0] + a[1] == b[0] for a, b in zip(flat[:-1], flat[1:])) and flat[-1][0] + flat[-1][1] == 665
-    assert all(w % 8 == 0 for _, w in flat[:-1])
-    per_rank = [sum(plan[k][g][1] for k in range(K)) for g in range(8)]
-    assert max(per_rank) - min(per_rank) <= 16
-    for world in (1, 2, 4):
-        K, plan = dc.piece_plan(665, world)
-        flat = [p for r in plan for p in r]
-        assert all(a[0] + a[1] == b[0] for a, b in zip(flat[:-1], flat[1:])) and flat[-1][0] + flat[-1][1] == 665
-        assert all(w % 8 == 0 for _, w in flat[:-1]) and plan[0][0][1] == 16 and max(w for _, w in flat) <= 64
-        per_rank = [sum(plan[k][g][1] for k in range(K)) for g in range(world)]
-        assert max(per_rank) - min(per_rank) <= 8
-    assert dc.piece_plan(9, 4) == (1, [[(0, 8), (8, 1), (9, 0), (9, 0)]])
+    assert K == 3 and [sum(w for _, w in r) for r in plan] == [128, 256, 281]
+    assert dc.piece_plan(665, 8, 3)[1][0][0] == (0, 28)  # explicit rounds (Python model only): equal rounds
+    assert dc.piece_plan(9, 4) == (1, [[(0, 3), (3, 2), (5, 2), (7, 2)]])
+    assert dc.piece_plan(0, 2) == (1, [[(0, 0), (0, 0)]])
 
 
 def _free_port():

@@ -1,0 +1,52 @@
+"""Multi-GPU parity on hardware, through the C ABI (csrc/dist.cu): both forms — one process per GPU over NCCL
+(zkgpu_dist_init / zkgpu_dist_commit, driven by zkevm_prover_b200.dist_commit.CDist) and one process driving all GPUs
+(zkgpu_init_multi + the ordinary zkgpu_extend_and_merkelize) — must give, word for word, the tree and the row shards of
+the 1-GPU path.  Skipped on boxes with fewer than 2 GPUs.  Each case runs in its own process (the job topology is
+process-global state of the library)."""
+import pathlib
+import subprocess
+import sys
+
+import pytest
+
+import zkevm_prover_b200 as zk
+
+pytestmark = pytest.mark.gpu
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+
+
+def ngpu():
+    try:
+        return zk.lib().zkgpu_device_count()
+    except Exception:
+        return 0
+
+
+def run(*args):
+    r = subprocess.run([sys.executable, str(ROOT / "tests" / "gpu_dist_worker.py")] + [str(a) for a in args], capture_output=True, text=True,
+                       timeout=900)
+    assert r.returncode == 0 and ": ok" in r.stdout, (r.stdout[-3000:] + r.stderr[-3000:])
+    return r.stdout
+
+
+@pytest.mark.parametrize("mode,log_n,c,log_b,extra", [
+    ("spawn", 16, 665, 1, ""),        # the headline width, device-resident pieces, peer stores fused into the LDE
+    ("spawn", 12, 45, 2, "host"),     # pinned host pieces: ramped rounds, blowup 4
+    ("spawn", 12, 9, 1, "nccl"),      # the ncclSend/ncclRecv fallback exchange, narrow pieces
+    ("multi", 16, 665, 1, ""),        # single process, host trace in, host extended trace + tree out
+    ("multi", 10, 3, 3, ""),          # rows of <= 4 words are copied, not hashed; blowup 8
+    ("multi", 12, 100, 1, "nccl"),
+])
+def test_two_gpus_match_one_gpu(mode, log_n, c, log_b, extra):
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = run(mode, 2, log_n, c, log_b, extra)
+    if not extra and mode == "spawn":
+        assert "peer_stores=True" in out or "peer_stores=False" in out
+
+
+def test_eight_gpus_match_one_gpu():
+    if ngpu() < 8:
+        pytest.skip("needs 8 GPUs")
+    run("spawn", 8, 14, 665, 1, "")
+    run("multi", 8, 14, 665, 1, "")

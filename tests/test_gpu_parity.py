@@ -299,8 +299,8 @@ def test_device_pointer_commit_matches_oracle():
 
 
 def test_narrow_high_blowup_shape():
-    """config #4 shape class (12 cols, blowup 16) at 2^13 rows."""
-    n, c, b = 1 << 13, 12, 16
+    """BASELINE.json configs[3] at its stated size: 2^17 -> 2^21 rows x 12 columns, blowup 16 (16 coset transforms)."""
+    n, c, b = 1 << 17, 12, 16
     a = O.fill(n * c, SEED, 4).reshape(n, c)
     ext = np.zeros((n * b, c), dtype=np.uint64)
     tree = np.zeros((2 * n * b - 1) * 4, dtype=np.uint64)
@@ -354,6 +354,15 @@ def test_reverse_permutation_matches_reference_semantics():
     assert_eq(a, src[[br(i, 6) for i in range(size)]], "in place")
     with pytest.raises(zk.ZkGpuError):
         zk.NTT_Goldilocks(size, 0, 2).reversePermutation(a, a, size, 0, ncols_all, ncols_all)
+    # and against the compiled unmodified reference (oracle/_ref, zkref_reverse_permutation) where it is present
+    from oracle_lib import Reference
+    R = Reference()
+    if R:
+        for size, ncols_all, off, nc, ext in ((1 << 10, 9, 0, 9, 1), (1 << 12, 13, 5, 4, 1), (1 << 11, 6, 1, 3, 2), (1 << 9, 8, 0, 8, 8)):
+            src = O.fill(size * ncols_all, SEED, 12).reshape(size, ncols_all)
+            dst = np.full((size, nc), 7, dtype=np.uint64)
+            zk.NTT_Goldilocks(size, 0, ext).reversePermutation(dst, src, size, off, nc, ncols_all)
+            assert_eq(dst, R.reverse_permutation(src, size, off, nc, ncols_all, ext), "vs reference %r" % ((size, ncols_all, off, nc, ext),))
 
 
 def test_group_proof_from_device_resident_tree():
@@ -541,3 +550,123 @@ def test_fri_fold_layer_vs_oracle_and_reference_outputs():
         tree = zk.MerkleTreeGL(n_groups, group * 3, auxh)
         tree.merkelize()
         assert_eq(tree.nodes, O.merkletree(auxh, group * 3, n_groups), "FRI layer tree")
+
+
+# ------------------------------------------------------------------------------------------------ pinned at full size
+def test_reference_bench_golden_root_2p23x128():
+    """The reference's only large-shape golden vector: the root of the 2^23-row x 128-column Fibonacci matrix asserted in
+    src/goldilocks/benchs/bench.cpp:406-443 (MERKLETREE_BENCH_AVX) and its batch twin :584-587 (batch_size (128+3)/4 = 32)."""
+    import ctypes
+    nrows, ncols = 1 << 23, 128
+    m = np.empty(nrows * ncols, dtype=np.uint64)
+    O.L.oracle_merkle_kat_matrix(m.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint64(nrows), ctypes.c_uint64(ncols))
+    small = merkle_kat_matrix(64, ncols)
+    assert_eq(m[:64 * ncols], small, "generator")
+    d = _dev(m)
+    tree = np.zeros((2 * nrows - 1) * 4, dtype=np.uint64)
+    import torch
+    d_tree = torch.zeros(tree.size, dtype=torch.int64, device="cuda")
+    zk.PoseidonGoldilocks.merkletree(d_tree, d, ncols, nrows)
+    zk.sync()
+    assert_eq(_host(d_tree)[-4:], hexwords(KATS["merkle_root_8388608x128"]["expected"]), "bench.cpp:440-443 root")
+    zk.PoseidonGoldilocks.merkletree_batch(d_tree, d, ncols, nrows, (ncols + 3) // 4)
+    zk.sync()
+    assert_eq(_host(d_tree)[-4:], hexwords(KATS["merkle_batch_root_8388608x128_b32"]["expected"]), "bench.cpp:584-587 batch root")
+
+
+def test_headline_against_reference_pin():
+    """BASELINE.json configs[1] at full size (2^23 x 665, blowup 2) against tests/golden/headline_pin.json, which
+    tools/pin_headline_root.py computed with the COMPILED REFERENCE strip by strip (SURVEY 8(d) option iii): the root,
+    1026 leaf digests, nodes of every level and 28 full rows of the extended trace.  Device-resident, the bench's path."""
+    import torch
+    pin = load_golden("headline_pin.json")
+    n, c, b = 1 << pin["log_rows"], pin["cols"], 1 << pin["log_blowup"]
+    torch.cuda.empty_cache()
+    free, _ = torch.cuda.mem_get_info()
+    if free < 142e9:
+        pytest.skip("needs 135 GB of device memory plus LDE scratch")
+    n_ext = n * b
+    d_in = torch.empty(n * c, dtype=torch.int64, device="cuda")
+    d_ext = torch.empty(n_ext * c, dtype=torch.int64, device="cuda")
+    d_tree = torch.empty((2 * n_ext - 1) * 4, dtype=torch.int64, device="cuda")
+    zk.fill(d_in, n * c, SEED, 0)
+    zk.extend_and_merkelize(zk.NTT_Goldilocks(n), d_ext, d_tree, d_in, n_ext, n, c)
+    zk.sync()
+    assert_eq(_host(d_tree[-4:]), hexwords(pin["root"]), "root")
+    off = 0
+    for lv in pin["levels"]:
+        idx = torch.tensor(lv["index"], device="cuda")
+        got = d_tree[off: off + lv["nodes"] * 4].view(-1, 4)[idx]
+        assert_eq(_host(got), hexwords([w for dgt in lv["digests"] for w in dgt]), "level %d nodes" % lv["level"])
+        off += lv["nodes"] * 4
+    idx = torch.tensor(pin["rows"]["index"], device="cuda")
+    got = d_ext.view(n_ext, c)[idx]
+    assert_eq(_host(got), hexwords([w for r in pin["rows"]["words"] for w in r]), "sampled rows of the extended trace")
+    del d_in, d_ext, d_tree
+    torch.cuda.empty_cache()
+
+
+def test_stage4_commit_on_device():
+    """SURVEY 8(f) N1, second half: stage 4 of Starks::genProof (starks.cpp:261-293) as one device-resident call —
+    INTT(NExt x qDim), shift/regroup qq2[k*qDeg+p] = qq1[p*N+k] * shiftIn^p, NTT(NExt x qDim*qDeg), merkelize — against the
+    committed outputs of the compiled reference (zkref_stage4: the reference's NTT_Goldilocks + Goldilocks3::mul), the
+    oracle, and the live reference where it travelled; host and device pointers."""
+    import torch
+    from oracle_lib import Reference
+    R = Reference()
+    for case in [c for c in DIFF["cases"] if c["op"] == "stage4"]:
+        ln, lb, qd, qg = case["log_n"], case["log_blowup"], case["q_dim"], case["q_deg"]
+        n, ne = 1 << ln, 1 << (ln + lb)
+        q = O.fill(ne * qd, SEED + 6, 0)
+        cm4 = np.zeros((ne, qd * qg), dtype=np.uint64)
+        tree = np.zeros((2 * ne - 1) * 4, dtype=np.uint64)
+        zk.stage4_commit(zk.NTT_Goldilocks(ne), cm4, tree, q, ne, n, qd, qg)
+        assert digest(cm4) == case["sha256"], case
+        assert ["%016x" % int(x) for x in tree[-4:]] == case["root"], case
+        want = O.stage4(q, ne, n, qd, qg)
+        assert_eq(cm4, want, "cm4_2ns vs oracle")
+        assert_eq(tree, O.merkletree(want, qd * qg, ne), "tree vs oracle")
+        d_q, d_cm4 = _dev(q), torch.zeros(ne * qd * qg, dtype=torch.int64, device="cuda")
+        d_tree = torch.zeros(tree.size, dtype=torch.int64, device="cuda")
+        zk.stage4_commit(None, d_cm4, d_tree, d_q, ne, n, qd, qg)
+        zk.sync()
+        assert_eq(_host(d_cm4), want, "device pointers")
+        assert_eq(_host(d_tree), tree, "device tree")
+    # a larger shape against the live reference / oracle: 2^18 -> 2^20, qDim 3, qDeg 2 (random non-canonical words)
+    rng = np.random.default_rng(5)
+    n, ne = 1 << 18, 1 << 20
+    q = rng.integers(0, 2**63, size=ne * 3, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+    cm4 = np.zeros((ne, 6), dtype=np.uint64)
+    zk.stage4_commit(None, cm4, None, q, ne, n, 3, 2)
+    assert_eq(cm4, (R if R else O).stage4(q, ne, n, 3, 2), "2^20 x 3, qDeg 2")
+    with pytest.raises(zk.ZkGpuError):
+        zk.stage4_commit(None, cm4, None, q, ne, n, 3, 8)  # qDeg > blowup
+
+
+def test_commit_cache_serves_the_unchanged_call_pair():
+    """starks.cpp:53-57 on one host buffer: extendPol then merkelize.  The second call must return the reference's tree
+    without a second upload (ZKGPU_PIPE_TRACE shows it), also after the cache was switched off and on again."""
+    n, c, b = 1 << 13, 45, 2
+    a = O.fill(n * c, SEED, 77).reshape(n, c)
+    want_ext = O.extend_pol(a, n * b)
+    want_tree = O.merkletree(want_ext, c, n * b)
+    ntt = zk.NTT_Goldilocks(n)
+    for fuse in (1, 0, 1):
+        zk._check(zk.lib().zkgpu_tune(2, fuse))
+        ext = np.zeros((n * b, c), dtype=np.uint64)
+        ntt.extendPol(ext, a, n * b, n, c)
+        assert_eq(ext, want_ext, "extendPol")
+        launches = zk.lib().zkgpu_launch_count()
+        mt = zk.MerkleTreeGL(n * b, c, ext)
+        mt.merkelize()
+        assert_eq(mt.nodes, want_tree, "merkelize after extendPol (fuse=%d)" % fuse)
+        assert (zk.lib().zkgpu_launch_count() == launches) == bool(fuse), "cache hit must launch nothing, a miss must hash"
+        mt.nodes[:] = 0
+        mt.merkelize()  # entry consumed: plain path
+        assert_eq(mt.nodes, want_tree, "second merkelize")
+    ext = np.zeros((n * b, c), dtype=np.uint64)
+    ntt.extendPol(ext, a, n * b, n, c)
+    ext[0, 0] ^= np.uint64(1)  # a fingerprint row changed: the stale tree must not be served
+    mt = zk.MerkleTreeGL(n * b, c, ext)
+    mt.merkelize()
+    assert_eq(mt.nodes, O.merkletree(ext, c, n * b), "modified buffer")

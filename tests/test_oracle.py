@@ -119,6 +119,12 @@ def test_against_committed_reference_outputs():
             assert digest(o) == case["sha256"], case
             for i, w in case["samples"].items():
                 assert int(o.reshape(-1)[int(i)]) == int(w, 16)
+        elif op == "stage4":
+            n, n_ext = 1 << case["log_n"], 1 << (case["log_n"] + case["log_blowup"])
+            q = _gen(n_ext * case["q_dim"], 6)
+            o = O.stage4(q, n_ext, n, case["q_dim"], case["q_deg"])
+            assert digest(o) == case["sha256"], case
+            assert [("%016x" % int(x)) for x in O.merkletree(o, case["q_dim"] * case["q_deg"], n_ext)[-4:]] == case["root"]
         else:
             raise AssertionError(op)
 
@@ -142,6 +148,16 @@ def test_against_live_reference():
     for rows, c, dim, batch in [(64, 13, 1, 0), (32, 5, 3, 0), (128, 3, 1, 0), (16, 50, 1, 16), (8, 0, 1, 0)]:
         a = rng.integers(0, 2**63, size=(rows, max(c * dim, 1)), dtype=np.uint64)
         assert (O.merkletree(a, c, rows, dim, batch) == R.merkletree(a, c, rows, dim, batch)).all()
+    for ln, lb, qd in [(5, 1, 2), (7, 2, 3), (4, 3, 5), (9, 1, 1)]:
+        q = rng.integers(0, 2**63, size=(1 << (ln + lb)) * 3, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+        assert (O.stage4(q, 1 << (ln + lb), 1 << ln, 3, qd) == R.stage4(q, 1 << (ln + lb), 1 << ln, 3, qd)).all()
+    for size, ncols_all, off, nc, ext in ((64, 7, 2, 3, 1), (128, 5, 0, 5, 4)):
+        src = rng.integers(0, P, size=(size, ncols_all), dtype=np.uint64)
+        got = R.reverse_permutation(src, size, off, nc, ncols_all, ext)
+        for i in range(size):
+            r = int(format(i, "0%db" % (size.bit_length() - 1))[::-1], 2)
+            want = src[r, off:off + nc] if (ext == 1 or r * ncols_all + off < (size // ext) * ncols_all) else np.zeros(nc, dtype=np.uint64)
+            assert (got[i] == want).all()
     for pb, nb in [(4, 2), (8, 4), (10, 5), (5, 5), (7, 0), (12, 8)]:
         a = rng.integers(0, 2**63, size=((1 << pb), 3), dtype=np.uint64) * np.uint64(2) + np.uint64(1)  # includes words >= p
         x = rng.integers(0, P, size=3, dtype=np.uint64)

@@ -18,7 +18,7 @@ import pathlib
 import numpy as np
 
 __all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL", "FRIProve",
-           "extend_and_merkelize", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
+           "extend_and_merkelize", "stage4_commit", "invalidate", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
 
 GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
 _HERE = pathlib.Path(__file__).resolve().parent
@@ -66,6 +66,8 @@ ABI_SYMBOLS = {
     "zkgpu_fri_transpose": (_int, [_vp, _vp, _u64, _u64]),
     "zkgpu_merkle_levels": (_int, [_vp, _u64]),
     "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
+    "zkgpu_invalidate": (_int, [_vp]),
+    "zkgpu_stage4_commit": (_int, [_vp, _vp, _vp, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_init_multi": (_int, [_int]),
     "zkgpu_nccl_unique_id": (_int, [_vp]),
     "zkgpu_dist_init": (_int, [_vp, _int, _int]),
@@ -136,10 +138,11 @@ def sync():
 
 
 def stage_ms():
-    """{'lde', 'leaves', 'nodes', 'h2d', 'd2h'} device times in ms of the last commit-type call."""
+    """{'lde', 'leaves', 'nodes', 'unused', 'total'} device times in ms of the last commit-type call (zkgpu.h: slot [3] is
+    unused, slot [4] is the whole call including host<->device copies when any pointer was a host pointer)."""
     out = (ctypes.c_float * 5)()
     _check(lib().zkgpu_stage_ms(out))
-    return dict(zip(("lde", "leaves", "nodes", "h2d", "d2h"), [float(v) for v in out]))
+    return dict(zip(("lde", "leaves", "nodes", "unused", "total"), [float(v) for v in out]))
 
 
 def fill(dst, n, seed=0x9E3779B97F4A7C15, offset=0):
@@ -276,6 +279,17 @@ class FRIProve:
     def getTransposed(aux, pol, degree, trasposeBits):
         """friProve.cpp:252-271 on 3-word elements."""
         _check(lib().zkgpu_fri_transpose(_ptr(aux), _ptr(pol), degree, trasposeBits))
+
+
+def stage4_commit(ntt_extended, cm4_2ns, tree, q_2ns, N_Extended, N, qDim, qDeg):
+    """Starks::genProof stage 4 (starks.cpp:261-293): INTT, shift/regroup, NTT, merkelize — one device-resident call."""
+    _check(lib().zkgpu_stage4_commit(ntt_extended._h if ntt_extended is not None else None, _ptr(cm4_2ns), _ptr(tree), _ptr(q_2ns),
+                                     N_Extended, N, qDim, qDeg))
+
+
+def invalidate(host_buffer=None):
+    """Drop commit-cache entries for this host buffer (None: all of them)."""
+    _check(lib().zkgpu_invalidate(_ptr(host_buffer)))
 
 
 def extend_and_merkelize(ntt, out_ext, tree, inp, N_Extended, N, ncols):

@@ -6,6 +6,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <mutex>
 #include <vector>
 
 namespace zk {
@@ -406,6 +408,22 @@ __global__ void __launch_bounds__(256) fri_fold_kernel(u64 *out, const u64 *coef
 #pragma unroll
     for (int k = 0; k < 3; k++) out[g * 3 + k] = res[k];
 }
+
+// Stage 4 of Starks::genProof, the loop between the two transforms (src/starkpil/starks.cpp:264-281):
+//   qq2[k*qDeg + p] = qq1[p*N + k] * shiftIn^p   (elements of qDim words, Goldilocks3::mul(Element&, Element&, Goldilocks::Element&)
+//   multiplies every word, goldilocks_cubic_extension.hpp:1887-1892), k < N, p < qDeg, shiftIn = (1/7)^N.
+// qq1 arrives UNSCALED from the inverse transform; sp[p] = shiftIn^p / NExt carries its 1/NExt.
+// Output: the N non-zero rows of the reference's NExt x (qDim*qDeg) matrix qq2; one thread per word.
+__global__ void __launch_bounds__(256) stage4_regroup_kernel(u64 *qq2, const u64 *qq1, u64 n, u32 q_dim, u32 q_deg, const u64 *sp)
+{
+    const u64 w = (u64)q_dim * q_deg, total = n * w;
+    for (u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (u64)gridDim.x * blockDim.x)
+    {
+        const u64 k = t / w;
+        const u32 j = (u32)(t - k * w), p = j / q_dim, d = j - p * q_dim;
+        qq2[t] = gl::mul(qq1[((u64)p * n + k) * q_dim + d], __ldg(sp + p));
+    }
+}
 static inline unsigned nblocks(u64 n, unsigned per) { return (unsigned)((n + per - 1) / per); }
 // getTransposed: aux[i*h + j] = pol[j*w + i] (3-word elements); one thread per destination word
 __global__ void __launch_bounds__(256) fri_transpose_kernel(u64 *aux, const u64 *pol, u64 w, u64 h)
@@ -416,6 +434,101 @@ __global__ void __launch_bounds__(256) fri_transpose_kernel(u64 *aux, const u64 
     aux[t] = pol[(j * w + i) * 3 + k];
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Commit cache: what lets UNCHANGED starks.cpp get the fused path.  The reference calls
+//     ntt.extendPol(p_cm1_2ns, p_cm1_n, NExt, N, ncols, buffer)        (starks.cpp:53)
+//     treesGL[0]->merkelize()  ->  merkletree(nodes, source = p_cm1_2ns) (starks.hpp:186, merkleTreeGL.cpp:37-44)
+// on the same host buffer.  While extendPol has each extended strip on the device anyway, it also runs the row sponge over
+// it (the commit pipeline; with host pointers the call is bound by the PCIe copies, so the hashing is hidden under them)
+// and finishes the node levels; the tree is remembered under the key (host pointer, rows, columns).  The merkletree call
+// that follows finds it and only copies 32*(2*NExt-1) bytes back instead of re-uploading the 89 GB extended trace.
+// A few rows of the output are kept as a fingerprint: if the caller changed the buffer in between (or calls
+// zkgpu_invalidate), the entry is dropped and the tree is computed from the data as usual.
+// ---------------------------------------------------------------------------------------------------
+struct Resident
+{
+    const u64 *host = nullptr; // key: the caller's extended-trace buffer
+    u64 nrows = 0, ncols = 0;
+    u64 *d_tree = nullptr;     // device copy of the finished tree (single-GPU path)
+    u64 *h_tree = nullptr;     // pinned host copy (multi-GPU path: every device wrote its slices)
+    std::vector<u64> rows_idx, rows_words;
+};
+static std::mutex g_cache_mu;
+static std::vector<Resident> g_cache; // process-wide: the key is a host pointer
+int g_fuse_commit = -1;               // -1: read ZKGPU_FUSE_COMMIT (default on)
+
+static bool fuse_enabled()
+{
+    if (g_fuse_commit < 0)
+    {
+        const char *e = getenv("ZKGPU_FUSE_COMMIT");
+        g_fuse_commit = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_fuse_commit != 0;
+}
+static void cache_free(Resident &r)
+{
+    if (r.d_tree) cudaFree(r.d_tree);
+    if (r.h_tree) cudaFreeHost(r.h_tree);
+    r.d_tree = r.h_tree = nullptr;
+}
+// drop every entry whose buffer overlaps [p, p + bytes)  (bytes == 0: exact pointer; p == nullptr: everything)
+static void cache_invalidate(const void *p, size_t bytes)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (size_t i = 0; i < g_cache.size();)
+    {
+        Resident &r = g_cache[i];
+        const char *a = (const char *)r.host, *b = a + r.nrows * r.ncols * sizeof(u64);
+        const bool hit = p == nullptr || (bytes == 0 ? p == (const void *)a : ((const char *)p < b && (const char *)p + bytes > a));
+        if (hit)
+        {
+            cache_free(r);
+            g_cache.erase(g_cache.begin() + i);
+        }
+        else
+            i++;
+    }
+}
+static void cache_fingerprint(Resident &r)
+{
+    const u64 picks[6] = {0, 1, r.nrows / 3, r.nrows / 2, r.nrows - 2, r.nrows - 1};
+    for (u64 i : picks)
+        if (i < r.nrows)
+        {
+            r.rows_idx.push_back(i);
+            r.rows_words.insert(r.rows_words.end(), r.host + i * r.ncols, r.host + (i + 1) * r.ncols);
+        }
+}
+static void cache_put(Resident &&r)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    while (g_cache.size() >= 4) // a genProof has at most a handful of commit stages in flight
+    {
+        cache_free(g_cache.front());
+        g_cache.erase(g_cache.begin());
+    }
+    g_cache.push_back(std::move(r));
+}
+// the entry for this buffer if it is still what extendPol wrote; removed from the cache (the caller owns it now)
+static bool cache_take(const u64 *host, u64 nrows, u64 ncols, Resident *out)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (size_t i = 0; i < g_cache.size(); i++)
+    {
+        Resident &r = g_cache[i];
+        if (r.host != host || r.nrows != nrows || r.ncols != ncols) continue;
+        bool same = true;
+        for (size_t k = 0; k < r.rows_idx.size() && same; k++)
+            same = memcmp(host + r.rows_idx[k] * ncols, r.rows_words.data() + k * ncols, ncols * sizeof(u64)) == 0;
+        if (same) *out = std::move(r);
+        else cache_free(r);
+        g_cache.erase(g_cache.begin() + i);
+        return same;
+    }
+    return false;
+}
 
 // "device pointers only" entry points: reject host pointers and mis-aligned digest arrays (the kernels access leaves and
 // tree as 16-byte ulonglong2) with rc < 0 instead of a sticky device fault
@@ -439,6 +552,18 @@ static int need_dev(const char *fn, const void *p, const char *what, bool align1
 using namespace zk;
 
 extern "C" {
+
+// ZKGPU_NGPU=n in the environment makes a single-process host (zkevm-prover itself) use n GPUs without any code change:
+// checked once, by the first commit-type call
+static void multi_from_env()
+{
+    static std::once_flag once;
+    std::call_once(once, []() {
+        const char *e = getenv("ZKGPU_NGPU");
+        if (e && atoi(e) > 1 && dist_world_of_process() == 0)
+            if (zkgpu_init_multi(atoi(e)) < 0) fprintf(stderr, "[zkgpu] ZKGPU_NGPU=%s ignored: %s\n", e, zkgpu_last_error());
+    });
+}
 
 int zkgpu_init(int device)
 {
@@ -748,6 +873,7 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
     if (n == 0 || ncols == 0 || n_ext == 0) return 0;
     unsigned log_n, log_b;
     ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
+    multi_from_env();
     ZK_ENTER;
     cudaStream_t st = C.cur;
     const bool dev = is_device_ptr(input);
@@ -767,12 +893,72 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
         C.timed = true;
         return 0;
     }
-    // host pointers: column strips, host->device of strip s+1 and device->host of strip s-1 overlap the LDE of strip s
-    ZK_TRY(commit_pipeline(C, output, false, nullptr, input, false, log_n, log_b, ncols, st));
-    ZK_CUDA(cudaEventRecord(C.ev[2], st));
-    ZK_CUDA(cudaEventRecord(C.ev[3], st));
-    C.timed = true;
-    ZK_CUDA(cudaStreamSynchronize(st));
+    // host pointers: column strips, host->device of strip s+1 and device->host of strip s-1 overlap the LDE of strip s.
+    // With the commit cache on, the strips are hashed on the way (see Resident above) for the merkelize() that follows.
+    cache_invalidate(output, n_ext * ncols * sizeof(u64));
+    if (dist_world_of_process() > 1 && fuse_enabled() && ncols > 4 && n_ext >= (u64)dist_world_of_process() && output != input)
+    {
+        // multi-GPU job (zkgpu_init_multi / ZKGPU_NGPU): all GPUs extend and hash; the tree waits in pinned host memory
+        en__.lk.unlock(); // the worker threads lock their own contexts, device 0's included
+        Resident r;
+        r.host = output;
+        r.nrows = n_ext;
+        r.ncols = ncols;
+        if (cudaMallocHost(&r.h_tree, (2 * n_ext - 1) * 4 * sizeof(u64)) != cudaSuccess)
+        {
+            set_error("extendPol: cannot allocate the pinned tree buffer: %s", cudaGetErrorString(cudaGetLastError()));
+            return -4;
+        }
+        const int rc = dist_multi_commit(output, r.h_tree, input, n_ext, n, ncols);
+        if (rc < 0)
+        {
+            cache_free(r);
+            return rc;
+        }
+        cache_fingerprint(r);
+        cache_put(std::move(r));
+        return 0;
+    }
+    u64 *d_tree = nullptr;
+    if (fuse_enabled() && ncols > 4)
+    {
+        if (cudaMalloc(&d_tree, (2 * n_ext - 1) * 4 * sizeof(u64)) != cudaSuccess)
+        {
+            cudaGetLastError();
+            d_tree = nullptr; // no room: plain extendPol
+        }
+    }
+    int rc = commit_pipeline(C, output, false, d_tree, input, false, log_n, log_b, ncols, st);
+    if (rc >= 0)
+    {
+        cudaEventRecord(C.ev[2], st);
+        if (d_tree) rc = merkle_levels(d_tree, n_ext, st);
+        cudaEventRecord(C.ev[3], st);
+        C.timed = true;
+    }
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (rc < 0 || e != cudaSuccess)
+    {
+        if (d_tree) cudaFree(d_tree);
+        if (rc >= 0) ZK_CUDA(e);
+        return rc;
+    }
+    if (d_tree)
+    {
+        Resident r;
+        r.host = output;
+        r.nrows = n_ext;
+        r.ncols = ncols;
+        r.d_tree = d_tree;
+        cache_fingerprint(r);
+        cache_put(std::move(r));
+    }
+    return 0;
+}
+
+int zkgpu_invalidate(const void *host_ptr)
+{
+    cache_invalidate(host_ptr, 0);
     return 0;
 }
 
@@ -815,12 +1001,41 @@ static int merkletree_impl(uint64_t *tree, const uint64_t *input, uint64_t ncols
         set_error("merkletree: num_rows %llu is not a power of two", (unsigned long long)nrows);
         return -1;
     }
-    ZK_ENTER;
-    cudaStream_t st = C.cur;
     const u64 row_words = ncols * dim;
     const u64 tree_words = (2 * nrows - 1) * 4;
-    const bool tree_dev = is_device_ptr(tree);
     const bool in_dev = row_words == 0 || is_device_ptr(input);
+    if (!in_dev && !batched)
+    {
+        // merkelize() of the buffer extendPol just produced: the tree is already there (commit cache)
+        Resident r;
+        if (cache_take(input, nrows, row_words, &r))
+        {
+            int rc = 0;
+            if (r.h_tree)
+            {
+                if (is_device_ptr(tree))
+                    rc = zkgpu_memcpy(tree, r.h_tree, tree_words * sizeof(u64));
+                else
+                    memcpy(tree, r.h_tree, tree_words * sizeof(u64));
+            }
+            else
+            {
+                Enter en(ptr_device(r.d_tree));
+                rc = en.rc;
+                if (rc >= 0 && cudaMemcpy(tree, r.d_tree, tree_words * sizeof(u64), cudaMemcpyDefault) != cudaSuccess)
+                {
+                    set_error("merkletree: copying the cached tree failed: %s", cudaGetErrorString(cudaGetLastError()));
+                    rc = -2;
+                }
+            }
+            cache_free(r);
+            if (getenv("ZKGPU_PIPE_TRACE")) fprintf(stderr, "[zkgpu cache] merkletree(%p): tree taken from the commit cache, no upload\n", (const void *)input);
+            return rc;
+        }
+    }
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
+    const bool tree_dev = is_device_ptr(tree);
     if (tree_dev && ((uintptr_t)tree & 15))
     {
         set_error("merkletree: a device tree pointer must be 16-byte aligned");
@@ -1010,6 +1225,7 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     unsigned log_n, log_b;
     ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
     // after zkgpu_init_multi a host-resident trace is committed by all GPUs of the job (dist.cu)
+    multi_from_env();
     if (dist_world_of_process() > 1 && ncols > 0 && !is_device_ptr(input) && n_ext >= (u64)dist_world_of_process())
         return dist_multi_commit(out_ext, tree, input, n_ext, n, ncols);
     ZK_ENTER;
@@ -1091,12 +1307,98 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
     return 0;
 }
 
+int zkgpu_stage4_commit(void *, uint64_t *cm4_2ns, uint64_t *tree, const uint64_t *q_2ns, uint64_t n_ext, uint64_t n, uint64_t q_dim,
+                        uint64_t q_deg)
+{
+    if (n == 0 || n_ext == 0 || q_dim == 0 || q_deg == 0) return 0;
+    unsigned log_n, log_b;
+    ZK_TRY(check_lde_args(n_ext, n, &log_n, &log_b));
+    if (q_deg > ((u64)1 << log_b) || q_deg > 64 || q_dim > 1024)
+    {
+        set_error("stage4: qDeg = %llu exceeds the blowup factor %llu (qq2 rows k*qDeg + p would leave the first N rows)",
+                  (unsigned long long)q_deg, (unsigned long long)1 << log_b);
+        return -1;
+    }
+    if (!cm4_2ns || !q_2ns)
+    {
+        set_error("stage4: NULL argument");
+        return -1;
+    }
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
+    const unsigned log_e = log_n + log_b;
+    const u64 w = q_dim * q_deg, in_words = n_ext * q_dim, out_words = n_ext * w, tree_words = (2 * n_ext - 1) * 4;
+    const bool dev = is_device_ptr(q_2ns);
+    if (dev != is_device_ptr(cm4_2ns))
+    {
+        set_error("stage4: cm4_2ns and q_2ns must both be host or both be device pointers");
+        return -1;
+    }
+    const bool tree_dev = tree == nullptr || is_device_ptr(tree);
+    if (tree && tree_dev && ((uintptr_t)tree & 15))
+    {
+        set_error("stage4: a device tree pointer must be 16-byte aligned");
+        return -1;
+    }
+    Staged din, dout, dtree;
+    const u64 *d_q = q_2ns;
+    u64 *d_out = cm4_2ns, *d_tree = tree;
+    if (!dev)
+    {
+        ZK_TRY(din.alloc(in_words));
+        ZK_TRY(dout.alloc(out_words));
+        ZK_CUDA(cudaMemcpyAsync(din.d, q_2ns, in_words * sizeof(u64), cudaMemcpyHostToDevice, st));
+        d_q = din.d;
+        d_out = dout.d;
+    }
+    if (tree && !tree_dev)
+    {
+        ZK_TRY(dtree.alloc(tree_words));
+        d_tree = dtree.d;
+    }
+    // scratch: qq1 (NExt x qDim) | qq2 (N x w) | transform scratch max(NExt*qDim, N*w) | sp (qDeg)
+    const u64 tmp_words = in_words > n * w ? in_words : n * w;
+    ZK_TRY(ctx_ensure_scratch(C, in_words + n * w + tmp_words + 64));
+    u64 *qq1 = C.scratch, *qq2 = qq1 + in_words, *tmp = qq2 + n * w, *sp = tmp + tmp_words;
+    ZK_CUDA(cudaEventRecord(C.ev[0], st));
+    Scale none;
+    ZK_TRY(ntt_transform(qq1, q_dim, d_q, q_dim, tmp, log_e, q_dim, true, none, none, st)); // nttExtended.INTT(qq1, q_2ns, NExt, qDim), x NExt
+    {
+        u64 h[64];
+        const u64 shift_in = gl::pow_slow(gl::pow_slow(GL_SHIFT, GL_P - 2), n); // Goldilocks::exp(inv(shift), N), starks.cpp:266
+        h[0] = gl::pow_slow(n_ext % GL_P, GL_P - 2);
+        for (u64 p = 1; p < q_deg; p++) h[p] = gl::mul_slow(h[p - 1], shift_in);
+        ZK_CUDA(cudaMemcpyAsync(sp, h, q_deg * sizeof(u64), cudaMemcpyHostToDevice, st));
+        ZK_CUDA(cudaStreamSynchronize(st)); // h[] is a stack buffer
+    }
+    u64 blocks = (n * w + 255) / 256;
+    if (blocks > (u64)C.num_sms * 32) blocks = (u64)C.num_sms * 32;
+    stage4_regroup_kernel<<<(unsigned)blocks, 256, 0, st>>>(qq2, qq1, n, (u32)q_dim, (u32)q_deg, sp);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    // nttExtended.NTT(cm4_2ns, qq2, NExt, qDim*qDeg) of the zero-padded rows = blowup coset transforms of size N
+    ZK_TRY(coset_ntts(d_out, w, qq2, w, tmp, log_n, log_b, w, 1, 1, st));
+    ZK_CUDA(cudaEventRecord(C.ev[1], st));
+    C.segs.clear();
+    if (tree)
+        ZK_TRY(merkle_all(d_tree, d_out, w, n_ext, st, C.ev[2]));
+    else
+        ZK_CUDA(cudaEventRecord(C.ev[2], st));
+    ZK_CUDA(cudaEventRecord(C.ev[3], st));
+    C.timed = true;
+    if (!dev) ZK_CUDA(cudaMemcpyAsync(cm4_2ns, d_out, out_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    if (tree && !tree_dev) ZK_CUDA(cudaMemcpyAsync(tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    if (!dev || (tree && !tree_dev)) ZK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
 int zkgpu_tune(int key, int value)
 {
     switch (key)
     {
     case 0: g_absorb_threads = value == 512 ? 512 : 128; return 0;
     case 1: g_ntt_threads_per_sm_cap = value < 0 ? 0 : value; return 0;
+    case 2: g_fuse_commit = value ? 1 : 0; return 0; // commit cache: extendPol with host pointers also hashes (default on)
     }
     set_error("zkgpu_tune: unknown key %d", key);
     return -1;

@@ -57,10 +57,13 @@ static int nccl_load()
 {
     std::lock_guard<std::mutex> lk(g_nccl_mu);
     if (g_nccl.h) return 0;
+    // Order: an explicit path; the libnccl.so.2 the process already holds (a Python host that imported torch has torch's
+    // bundled NCCL mapped: share it rather than map a second, possibly older, copy under the same soname); the system's.
     void *h = nullptr;
-    if (const char *p = getenv("ZKGPU_NCCL_LIB")) h = dlopen(p, RTLD_NOW | RTLD_GLOBAL);
-    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (const char *p = getenv("ZKGPU_NCCL_LIB")) h = dlopen(p, RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
     if (!h)
     {
         set_error("zkgpu: cannot load NCCL (libnccl.so.2): %s", dlerror());
@@ -431,7 +434,17 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
 
     ctx_pipe_event(C, nullptr, st);
     C.segs.clear();
+    // ZKGPU_DIST_TRACE=1: timeline of this rank's copies, transforms, barriers and sponge strips (development aid)
+    static const bool trace = getenv("ZKGPU_DIST_TRACE") != nullptr;
+    struct Mark { const char *what; int k, e; };
+    std::vector<Mark> marks;
+    auto mark = [&](const char *what, int k, cudaStream_t s) {
+        if (!trace) return;
+        int e = -1;
+        if (ctx_pipe_event(C, &e, s) >= 0) marks.push_back({what, k, e});
+    };
     ZK_CUDA(cudaEventRecord(C.ev[4], st));
+    mark("call", 0, st);
     // nobody may still be reading its rows (previous commit) when a peer starts storing into them
     ZK_TRY(dist_barrier(D, st, st, D.ev_a, D.ev_b));
 
@@ -439,9 +452,13 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         const int b = k & 1;
         const u64 w = pl.w[k][me];
         if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(C.h2d, C.in_free[b], 0));
-        if (w)
+        mark("h2d+", k, C.h2d);
+        if (w && pieces[k].ld == w)
+            ZK_CUDA(cudaMemcpyAsync(D.in_buf + (size_t)b * n * wmax, pieces[k].p, n * w * sizeof(u64), cudaMemcpyHostToDevice, C.h2d));
+        else if (w)
             ZK_CUDA(cudaMemcpy2DAsync(D.in_buf + (size_t)b * n * wmax, w * sizeof(u64), pieces[k].p, pieces[k].ld * sizeof(u64), w * sizeof(u64), n,
                                       cudaMemcpyHostToDevice, C.h2d));
+        mark("h2d-", k, C.h2d);
         ZK_CUDA(cudaEventRecord(C.in_ready[b], C.h2d));
         return 0;
     };
@@ -480,6 +497,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
             ZK_TRY(merkle_absorb(D.sub, D.rows + pl.round_c0[k], pl.round_w[k], ncols, R, k == 0, st));
             ZK_TRY(ctx_pipe_event(C, &e1, st));
             C.segs.push_back({1, e0, e1});
+            mark("abs-", k, st);
         }
         return 0;
     };
@@ -504,6 +522,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
             src_ld = w;
         }
         int e0, e1;
+        mark("lde+", k, st);
         ZK_TRY(ctx_pipe_event(C, &e0, st));
         u64 *ext = D.p2p ? nullptr : D.ext_buf + (size_t)b * n_ext * wmax;
         if (w)
@@ -522,6 +541,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         }
         ZK_TRY(ctx_pipe_event(C, &e1, st));
         C.segs.push_back({0, e0, e1});
+        mark("lde-", k, st);
         if (host_input) ZK_CUDA(cudaEventRecord(C.in_free[b], st));
         // exchange point of round k
         ZK_CUDA(cudaEventRecord(D.ev_lde[k], st));
@@ -542,6 +562,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
             ZK_NCCL(g_nccl.GroupEnd());
         }
         ZK_CUDA(cudaEventRecord(D.ev_bar[k], D.cs));
+        mark("bar-", k, D.cs);
         if (k > 0) ZK_TRY(absorb_round(k - 1));
     }
     if (pl.rounds > 0) ZK_TRY(absorb_round(pl.rounds - 1));
@@ -601,10 +622,25 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         ZK_CUDA(cudaStreamWaitEvent(st, C.out_free[0], 0));
     }
     ZK_CUDA(cudaEventRecord(C.ev[5], st));
-    if (host_input || ext_host || (tree && !tree_is_dev))
+    mark("end", 0, st);
+    if (host_input || ext_host || (tree && !tree_is_dev) || trace)
     {
         ZK_CUDA(cudaStreamSynchronize(st));
         ZK_CUDA(cudaEventElapsedTime(&C.stage[4], C.ev[4], C.ev[5]));
+    }
+    if (trace && !marks.empty())
+    {
+        ZK_CUDA(cudaStreamSynchronize(C.h2d));
+        ZK_CUDA(cudaStreamSynchronize(D.cs));
+        char line[4096];
+        int o = snprintf(line, sizeof(line), "[zkgpu dist] rank %d timeline (ms):", me);
+        for (auto &m : marks)
+        {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, C.pool[marks[0].e], C.pool[m.e]);
+            if (o < (int)sizeof(line) - 32) o += snprintf(line + o, sizeof(line) - o, " %s%d=%.1f", m.what, m.k, ms);
+        }
+        fprintf(stderr, "%s\n", line);
     }
     return 0;
 }

@@ -574,32 +574,51 @@ int ntt_transform(u64 *dst, u64 dst_ld, const u64 *src, u64 src_ld, u64 *tmp, un
     return 0;
 }
 
+// b = 2^log_blowup transforms of size N over the cosets g0 * w_ext^r of the extended domain, written interleaved into its
+// natural order:  out[(k << log_blowup) + r] = scale * sum_i coef_i (g0 w_ext^r)^i w_N^(ik).
+// This is the forward NTT of size N*b of the zero-padded coefficient rows (times the powers of g0) without ever touching
+// the zero rows (the reference transforms them: ntt_goldilocks.cpp:259-277).
+int coset_ntts(u64 *out, u64 out_ld, const u64 *coef, u64 coef_ld, u64 *tmp, unsigned log_n, unsigned log_blowup, u64 ncols, u64 g0,
+               u64 scale, cudaStream_t st, const Scatter *sc)
+{
+    const u64 b = (u64)1 << log_blowup;
+    const u64 wext = gl::root_of_unity(log_n + log_blowup);
+    Scale none;
+    u64 g = g0 % GL_P; // coset r: g_r = g0 * w_ext^r
+    for (u64 r = 0; r < b; r++)
+    {
+        Scale pre;
+        if (g != 1)
+        {
+            pre.mode = SCALE_POWER;
+            ZK_TRY(get_power_tables(g, scale, log_n, &pre.G0, &pre.G1, st));
+        }
+        else if (scale != 1)
+        {
+            pre.mode = SCALE_CONST;
+            pre.konst = scale;
+        }
+        if (sc)
+            ZK_TRY(ntt_transform(nullptr, 0, coef, coef_ld, tmp, log_n, ncols, false, pre, none, st, sc, log_blowup, (unsigned)r));
+        else
+            ZK_TRY(ntt_transform(out + r * out_ld, out_ld * b, coef, coef_ld, tmp, log_n, ncols, false, pre, none, st));
+        g = gl::mul_slow(g, wext);
+    }
+    return 0;
+}
+
 int lde_strip(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, u64 *scratch, unsigned log_n, unsigned log_blowup,
               u64 ncols, cudaStream_t st, const Scatter *sc)
 {
     if (ncols == 0) return 0;
     const u64 n = (u64)1 << log_n;
-    const u64 b = (u64)1 << log_blowup;
     u64 *coef = scratch;
     u64 *tmp = scratch + n * ncols;
     Scale none;
     // unscaled inverse transform: coef_i * N   (1/N is folded into the coset tables)
     ZK_TRY(ntt_transform(coef, ncols, in, in_ld, tmp, log_n, ncols, true, none, none, st));
     const u64 ninv = gl::pow_slow(n % GL_P, GL_P - 2);
-    const u64 wext = gl::root_of_unity(log_n + log_blowup);
-    u64 g = GL_SHIFT; // coset r: g_r = 7 * w_ext^r
-    for (u64 r = 0; r < b; r++)
-    {
-        Scale pre;
-        pre.mode = SCALE_POWER;
-        ZK_TRY(get_power_tables(g, ninv, log_n, &pre.G0, &pre.G1, st));
-        if (sc)
-            ZK_TRY(ntt_transform(nullptr, 0, coef, ncols, tmp, log_n, ncols, false, pre, none, st, sc, log_blowup, (unsigned)r));
-        else
-            ZK_TRY(ntt_transform(out + r * out_ld, out_ld * b, coef, ncols, tmp, log_n, ncols, false, pre, none, st));
-        g = gl::mul_slow(g, wext);
-    }
-    return 0;
+    return coset_ntts(out, out_ld, coef, ncols, tmp, log_n, log_blowup, ncols, GL_SHIFT, ninv, st, sc);
 }
 
 } // namespace zk

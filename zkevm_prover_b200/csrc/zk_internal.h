@@ -144,6 +144,9 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
 int lde_strip(u64 *out, u64 out_ld, const u64 *in, u64 in_ld, u64 *scratch, unsigned log_n, unsigned log_blowup,
               u64 ncols, cudaStream_t st, const Scatter *sc = nullptr);
 
+int coset_ntts(u64 *out, u64 out_ld, const u64 *coef, u64 coef_ld, u64 *tmp, unsigned log_n, unsigned log_blowup, u64 ncols, u64 g0,
+               u64 scale, cudaStream_t st, const Scatter *sc = nullptr);
+
 // ---- Poseidon / Merkle (poseidon.cu) ----
 int poseidon_init_constants();
 // leaves: tree[4*i .. 4*i+3] = linear_hash(input row i), rows of row_words words with stride row_ld

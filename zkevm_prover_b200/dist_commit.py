@@ -1,4 +1,13 @@
-"""Multi-GPU commit stage: one process per GPU, torch.distributed for the plumbing.
+"""Multi-GPU commit stage, host side.
+
+The product path is in the library (csrc/dist.cu behind include/zkgpu.h): `CDist` below is the thin driver a
+process-per-GPU launcher (torchrun) needs — it hands NCCL's unique id to the other ranks through torch.distributed and
+then calls zkgpu_dist_init / zkgpu_dist_commit; single-process hosts call zkgpu_init_multi and the ordinary
+zkgpu_extend_and_merkelize instead.
+
+`commit_sharded` / `commit_sharded_pipelined` are the same pipeline spelled in Python over injected compute steps
+(`ops`): the host-logic model the CPU test-suite runs over gloo with the oracle standing in for the device steps, and a
+second implementation (torch.distributed all-to-all instead of peer stores) the GPU tests compare the library against.
 
   1. the trace is column-sharded (NTT columns are independent, ntt_goldilocks.cpp:103-110): rank g owns columns
      [cuts[g], cuts[g+1]) as an N x C_g row-major matrix and extends it to NExt x C_g (zkgpu_lde_columns);
@@ -42,6 +51,8 @@ class GpuOps:
         import torch
         import zkevm_prover_b200 as zk
         self.torch, self.zk = torch, zk
+        # the library must enqueue on the stream torch orders its collectives, copies and allocator frees against
+        zk.set_stream(torch.cuda.current_stream())
 
     def empty(self, nwords):
         return self.torch.empty(nwords, dtype=self.torch.int64, device="cuda")
@@ -132,36 +143,34 @@ def exchange_async(dist, send, recv, send_splits, recv_splits, group=None):
     return _Done()
 
 
-def piece_plan(ncols, world, rounds=None):
-    """Column ownership of the pipelined commit: the row is cut into rounds x world consecutive pieces, piece (k, g)
-    belonging to rank g in round k, every piece a whole number of 8-column sponge blocks (the last one holds the ragged
-    tail).  Returns (rounds, plan) with plan[k][g] = (first column, width).
+def piece_plan(ncols, world, rounds=None, host_input=True):
+    """Column ownership of the pipelined commit (zkgpu_dist_plan, csrc/dist.cu make_plan): the row is cut into
+    rounds x world consecutive pieces, piece (k, g) belonging to rank g in round k.  Every round but the last covers a
+    whole number of 8-column sponge blocks; inside a round the columns are dealt out evenly (the extra columns rotate
+    over the ranks from round to round).  Returns (rounds, plan) with plan[k][g] = (first column, width).
 
-    With rounds=None the rounds ramp up: 2 blocks per rank, then 4, then the rest in equal rounds of at most 8 blocks
-    per rank — with a host-resident trace only the copy of the first (small) piece is exposed and each later copy fits
-    under the compute of the round before it (same reasoning as the single-GPU strip ramp, csrc/api.cu).
-    665 columns on 8 ranks: 3 rounds of 16-, 32- and 40/32-column pieces.  An explicit `rounds` gives equal rounds."""
+    host_input=True: the rounds ramp up — 2 blocks per rank, then 4, then equal rounds of at most 8 — so that with a
+    host-resident trace only the copy of the first small piece is exposed; host_input=False: one round.
+    An explicit `rounds` gives equal rounds (test hook, Python model only)."""
+    if rounds is None:
+        import ctypes
+        import zkevm_prover_b200 as zk
+        r = ctypes.c_int(0)
+        c0 = (ctypes.c_uint64 * (16 * world))()
+        w = (ctypes.c_uint64 * (16 * world))()
+        zk._check(zk.lib().zkgpu_dist_plan(ncols, world, int(host_input), ctypes.byref(r), c0, w))
+        return r.value, [[(int(c0[k * world + g]), int(w[k * world + g])) for g in range(world)] for k in range(r.value)]
     blocks = -(-ncols // 8)
-    if rounds is not None:
-        per_round = [blocks // rounds + (1 if k < blocks % rounds else 0) for k in range(rounds)]
-    else:
-        per_round, left = [], blocks
-        for want in (2 * world, 4 * world):
-            if left >= want + 4 * world:
-                per_round.append(want)
-                left -= want
-        k = max(1, -(-left // (8 * world)))
-        per_round += [left // k + (1 if i < left % k else 0) for i in range(k)]
-        rounds = len(per_round)
-    plan, c0, rot = [], 0, 0
+    per_round = [blocks // rounds + (1 if k < blocks % rounds else 0) for k in range(rounds)]
+    plan, c, rot = [], 0, 0
     for nb in per_round:
-        base, extra = divmod(nb, world)
+        cols = min(nb * 8, ncols - c)
+        base, extra = divmod(cols, world)
         row = []
         for g in range(world):
-            # the odd blocks of a round go to a different group of ranks each round, so that column counts stay level
-            w = min((base + (1 if (g - rot) % world < extra else 0)) * 8, ncols - c0)
-            row.append((c0, w))
-            c0 += w
+            wg = base + (1 if (g - rot) % world < extra else 0)
+            row.append((c, wg))
+            c += wg
         plan.append(row)
         rot = (rot + extra) % world
     return rounds, plan
@@ -200,12 +209,16 @@ def commit_sharded_pipelined(ops, dist, pieces_in, n, n_ext, ncols, rounds=None,
     recv_buf = [ops.empty(max(R * wmax_round, 1)) for _ in range(min(2, rounds))]
 
     def finish(k, recv):
+        # unpack the G received blocks into the row-major row shard, then absorb the round's columns from there
         off = 0
         for g in range(world):
             c0, w = plan[k][g]
             if w:
-                ops.absorb(sub, recv, off, w, w, R, k == 0 and g == 0, rows, c0, ncols)
+                ops.copy_block(rows, c0, ncols, recv, off, w, R, w)
             off += R * w
+        c0, wr = plan[k][0][0], sum(w for _, w in plan[k])
+        if wr:
+            ops.absorb(sub, rows, c0, wr, ncols, R, k == 0)
         mark("leaves")
 
     pending = None
@@ -305,3 +318,52 @@ def commit_sharded(ops, dist, local_in, n, n_ext, ncols, group=None, timers=None
     tree = _gather_and_stitch(ops, dist, sub, tree, R, n_ext, group)
     mark("nodes")
     return rows, tree
+
+
+class CDist:
+    """Driver of the library's process-per-GPU form (include/zkgpu.h: zkgpu_dist_init / zkgpu_dist_commit).
+
+    torch.distributed is used for one thing: rank 0's NCCL unique id travels to the other ranks.  Everything else —
+    the column plan, the LDE with its peer stores, the barriers, the sponge, the stitch — happens inside libzkgpu.so."""
+
+    def __init__(self, dist, device, group=None):
+        import ctypes
+        import torch
+        import zkevm_prover_b200 as zk
+        self.zk, self.torch, self.ct = zk, torch, ctypes
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        zk.init(device)
+        uid = ctypes.create_string_buffer(128)
+        if self.rank == 0:
+            zk._check(zk.lib().zkgpu_nccl_unique_id(uid))
+        box = [bytes(uid.raw)]
+        dist.broadcast_object_list(box, src=0, group=group)
+        uid = ctypes.create_string_buffer(box[0], 128)
+        zk._check(zk.lib().zkgpu_dist_init(uid, self.rank, self.world))
+
+    def plan(self, ncols, host_input=False):
+        return piece_plan(ncols, self.world, None, host_input)
+
+    def commit(self, pieces, n, n_ext, ncols, tree=None, host_input=False, gather=True, ld=None):
+        """pieces[k]: this rank's N x w(k, rank) piece of round k (torch tensors: CUDA, or pinned host with host_input).
+        tree: rank 0's destination tensor / array when gather is set."""
+        ct, zk = self.ct, self.zk
+        K = len(pieces)
+        ptrs = (ct.c_void_p * K)(*[zk._ptr(p) for p in pieces])
+        rounds, plan = self.plan(ncols, host_input)
+        assert rounds == K, "pieces do not match zkgpu_dist_plan"
+        lds = (ct.c_uint64 * K)(*[(ld[k] if ld else plan[k][self.rank][1]) for k in range(K)])
+        zk._check(zk.lib().zkgpu_dist_commit(None, zk._ptr(tree), ptrs, lds, int(host_input), int(gather), n_ext, n, ncols))
+
+    def rows(self):
+        """(address of this rank's R x ncols row shard, R, ncols, address of its subtree) — library-owned device memory."""
+        ct = self.ct
+        p, sub, r, c = ct.c_void_p(), ct.c_void_p(), ct.c_uint64(), ct.c_uint64()
+        self.zk._check(self.zk.lib().zkgpu_dist_rows(ct.byref(p), ct.byref(r), ct.byref(c), ct.byref(sub)))
+        return p.value, r.value, c.value, sub.value
+
+    def peer_stores(self):
+        ct = self.ct
+        a, b, c = ct.c_int(), ct.c_int(), ct.c_int()
+        self.zk._check(self.zk.lib().zkgpu_dist_info(ct.byref(a), ct.byref(b), ct.byref(c)))
+        return bool(c.value)
