@@ -5,8 +5,10 @@
 #include <cstdarg>
 #include <vector>
 namespace zk {
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 void set_error(const char *fmt, ...) { va_list ap; va_start(ap, fmt); vfprintf(stderr, fmt, ap); va_end(ap); fputc('\n', stderr); }
+static Ctx g_bench_ctx;
+thread_local Ctx *t_ctx = &g_bench_ctx;
 }
 int main()
 {
