@@ -37,7 +37,8 @@ const char *zkgpu_last_error(void);
 int zkgpu_device_count(void);
 uint64_t zkgpu_launch_count(void);     /* kernels this library has launched so far in this process */
 int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes);
-/* tuning / experiment hook: key 0 = threads per CTA of the sponge kernel (128 | 512), key 1 = cap on transform threads per
+/* tuning / experiment hook: key 0 = threads per CTA of the sponge kernel (128 | 512), key 2 = commit cache on/off, key 3 = largest
+ * tree level (parents) hashed by the cooperative 16-lanes-per-hash kernel (0 = never), key 1 = cap on transform threads per
  * SM (0 = none).  Used by tools/overlap_probe.py; not needed in normal use. */
 int zkgpu_tune(int key, int value);
 /* device-memory helpers so that C/C++ hosts need no CUDA headers */
@@ -187,11 +188,12 @@ int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64
  *     After the call zkgpu_dist_rows gives this rank's row shard of the extended trace (rows [rank*R, (rank+1)*R), R = NExt /
  *     world, row-major with ncols columns: the layout MerkleTreeGL::source has) and its subtree ((2R-1)*4 words).
  * The column-shard -> row-shard exchange is done by the LDE's own stores into the peers' row shards over NVLink (peer
- * access / CUDA IPC); without peer access, or with ZKGPU_EXCHANGE=nccl, by grouped ncclSend/ncclRecv per round. */
+ * access / CUDA IPC); ZKGPU_EXCHANGE=dma stages the rows locally and lets the copy engines push them to the peers; without
+ * peer access, or with ZKGPU_EXCHANGE=nccl, grouped ncclSend/ncclRecv per round do it. */
 int zkgpu_init_multi(int ngpu);
 int zkgpu_nccl_unique_id(void *out128);
 int zkgpu_dist_init(const void *nccl_unique_id, int rank, int world);
-int zkgpu_dist_info(int *rank, int *world, int *peer_stores);
+int zkgpu_dist_info(int *rank, int *world, int *exchange); /* exchange: 1 = peer stores fused into the LDE, 2 = copy engines, 0 = NCCL */
 int zkgpu_dist_plan(uint64_t ncols, int world, int host_input, int *rounds, uint64_t *c0, uint64_t *w);
 int zkgpu_dist_commit(void *ntt, uint64_t *tree, const uint64_t *const *pieces, const uint64_t *piece_ld, int host_input, int gather_tree,
                       uint64_t n_extended, uint64_t n, uint64_t ncols);

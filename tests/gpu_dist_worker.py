@@ -61,7 +61,7 @@ def spawn_rank(rank, world, log_n, c, log_b, port, host_input, exchange):
                 got = tree.cpu().numpy().view(np.uint64)
                 bad = np.nonzero(got != want_tree)[0]
                 assert bad.size == 0, "tree differs at %d words, first %d (rep %d)" % (bad.size, bad[0], rep)
-        print("rank %d ok: peer_stores=%s rounds=%d" % (rank, cd.peer_stores(), K), flush=True)
+        print("rank %d ok: exchange=%s rounds=%d" % (rank, cd.exchange(), K), flush=True)
     finally:
         dist.destroy_process_group()
 
@@ -76,11 +76,14 @@ def main():
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
         s.close()
-        mp.spawn(spawn_rank, args=(world, log_n, c, log_b, port, "host" in extra, "nccl" if "nccl" in extra else ""), nprocs=world, join=True)
+        mp.spawn(spawn_rank, args=(world, log_n, c, log_b, port, "host" in extra, "nccl" if "nccl" in extra else "dma" if "dma" in extra else ""),
+                 nprocs=world, join=True)
         print("dist spawn: ok")
     elif mode == "multi":
         if "nccl" in extra:
             os.environ["ZKGPU_EXCHANGE"] = "nccl"
+        if "dma" in extra:
+            os.environ["ZKGPU_EXCHANGE"] = "dma"
         import torch  # before the library maps an NCCL: torch's own libnccl.so.2 must be the one this process holds
         import zkevm_prover_b200 as zk
         from oracle_lib import Oracle

@@ -33,6 +33,9 @@ def run(*args):
     ("spawn", 16, 665, 1, ""),        # the headline width, device-resident pieces, peer stores fused into the LDE
     ("spawn", 12, 45, 2, "host"),     # pinned host pieces: ramped rounds, blowup 4
     ("spawn", 12, 9, 1, "nccl"),      # the ncclSend/ncclRecv fallback exchange, narrow pieces
+    ("spawn", 14, 100, 1, "dma"),     # staged exchange by the copy engines, three rounds
+    ("spawn", 12, 45, 2, "dma host"),
+    ("multi", 13, 77, 1, "dma"),
     ("multi", 16, 665, 1, ""),        # single process, host trace in, host extended trace + tree out
     ("multi", 10, 3, 3, ""),          # rows of <= 4 words are copied, not hashed; blowup 8
     ("multi", 12, 100, 1, "nccl"),
@@ -41,8 +44,8 @@ def test_two_gpus_match_one_gpu(mode, log_n, c, log_b, extra):
     if ngpu() < 2:
         pytest.skip("needs 2 GPUs")
     out = run(mode, 2, log_n, c, log_b, extra)
-    if not extra and mode == "spawn":
-        assert "peer_stores=True" in out or "peer_stores=False" in out
+    if mode == "spawn":
+        assert "exchange=" + ("nccl" if "nccl" in extra else "dma" if "dma" in extra else "") in out
 
 
 def test_eight_gpus_match_one_gpu():

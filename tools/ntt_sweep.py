@@ -27,8 +27,11 @@ def timeit(fn, reps=5):
 
 
 print("# log2(rows) cols | NTT ms GB/s frac | INTT ms GB/s frac | extendPol(b=2) ms GB/s frac   (peak %.0f GB/s measured copy)" % peak)
-for lg in (12, 14, 16, 18, 20, 22, 24):
-    for c in (1, 3, 8, 32, 100, 128, 665, 1024):
+import os
+COLS = tuple(int(x) for x in os.environ.get("NTT_SWEEP_COLS", "1,3,8,32,100,128,665,1024").split(","))
+LOGS = tuple(int(x) for x in os.environ.get("NTT_SWEEP_LOGS", "12,14,16,18,20,22,24").split(","))
+for lg in LOGS:
+    for c in COLS:
         n = 1 << lg
         if n * c * 8 * 4 > 60e9 or n * c < (1 << 16):
             continue

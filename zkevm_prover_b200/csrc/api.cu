@@ -127,13 +127,19 @@ static int lde_all(Ctx &C, u64 *out, u64 out_ld, const u64 *in, u64 in_ld, unsig
 {
     if (ncols == 0) return 0;
     const u64 n = (u64)1 << log_n;
-    size_t free_b = 0, total_b = 0;
-    ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    free_b += C.scratch_words * sizeof(u64);
-    size_t budget = (size_t)(0.6 * (double)free_b);
-    const size_t cap = (size_t)16 << 30;
-    if (budget > cap) budget = cap;
-    u64 w = budget / (2 * n * sizeof(u64));
+    u64 w = ncols;
+    // the whole width fits the scratch already held: no need to ask the driver (cudaMemGetInfo costs ~1 ms, which is most
+    // of the host time of a small commit)
+    if (2 * n * ncols > C.scratch_words)
+    {
+        size_t free_b = 0, total_b = 0;
+        ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        free_b += C.scratch_words * sizeof(u64);
+        size_t budget = (size_t)(0.6 * (double)free_b);
+        const size_t cap = (size_t)16 << 30;
+        if (budget > cap) budget = cap;
+        w = budget / (2 * n * sizeof(u64));
+    }
     if (w >= ncols)
         w = ncols;
     else
@@ -201,14 +207,18 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
     ZK_TRY(ctx_pipe_streams(C));
     // ---- strip width from the memory budget: per column 2n words of LDE scratch, 2n per host-input buffer pair,
     //      2*NExt per host-output buffer pair
-    size_t free_b = 0, total_b = 0;
-    ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    free_b += C.scratch_words * sizeof(u64);
-    size_t budget = (size_t)(0.6 * (double)free_b);
-    const size_t cap = (size_t)24 << 30;
-    if (budget > cap) budget = cap;
     const u64 per_col = 2 * n + (in_dev ? 0 : 2 * n) + (out_dev ? 0 : 2 * n_ext);
-    u64 w = budget / (per_col * sizeof(u64));
+    u64 w = ncols;
+    if (per_col * ncols > C.scratch_words) // see lde_all: ask the driver only when the scratch has to grow
+    {
+        size_t free_b = 0, total_b = 0;
+        ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        free_b += C.scratch_words * sizeof(u64);
+        size_t budget = (size_t)(0.6 * (double)free_b);
+        const size_t cap = (size_t)24 << 30;
+        if (budget > cap) budget = cap;
+        w = budget / (per_col * sizeof(u64));
+    }
     if (!in_dev || !out_dev)
     {
         // enough strips for the copies to overlap the compute
@@ -1398,6 +1408,7 @@ int zkgpu_tune(int key, int value)
     {
     case 0: g_absorb_threads = value == 512 ? 512 : 128; return 0;
     case 1: g_ntt_threads_per_sm_cap = value < 0 ? 0 : value; return 0;
+    case 3: g_coop_max_parents = value < 0 ? 0 : value; return 0; // 0: one thread per hash on every level
     case 2: g_fuse_commit = value ? 1 : 0; return 0; // commit cache: extendPol with host pointers also hashes (default on)
     }
     set_error("zkgpu_tune: unknown key %d", key);

@@ -96,6 +96,26 @@ static int nccl_load()
 // ---------------------------------------------------------------------------------------------------
 static const int MAX_WORLD = 16, MAX_ROUNDS = 16;
 
+// How the extended rows travel from the rank that computed them (column pieces) to the rank that hashes them (row shards):
+//   EX_STORES  the last pass of every coset transform stores each row straight into its owner's shard (peer memory over
+//              NVLink): one kernel does the transform and the exchange, one round, no staging buffer;
+//   EX_DMA     the transform writes a local staging buffer and the copy engines push the row blocks to the peers
+//              (cudaMemcpy2DAsync device-to-device over NVLink) while the SMs extend the next round / hash the previous one;
+//   EX_NCCL    grouped ncclSend/ncclRecv per round into a receive buffer that is then unpacked (no peer access needed).
+// ZKGPU_EXCHANGE=stores|dma|nccl picks one; default stores when every pair of GPUs has peer access, else nccl.
+enum { EX_STORES = 0, EX_DMA = 1, EX_NCCL = 2 };
+static int exchange_wanted()
+{
+    static const int w = []() {
+        const char *e = getenv("ZKGPU_EXCHANGE");
+        if (e && !strcmp(e, "nccl")) return (int)EX_NCCL;
+        if (e && !strcmp(e, "dma")) return (int)EX_DMA;
+        return (int)EX_STORES;
+    }();
+    return w;
+}
+static int g_exchange = EX_STORES; // what the job actually uses (set when peer access is known); read by zkgpu_dist_plan
+
 struct Dist
 {
     int rank = 0, world = 1;
@@ -103,6 +123,8 @@ struct Dist
     bool p2p = false, p2p_tried = false;
     ncclComm_t comm = nullptr;
     cudaStream_t cs = nullptr; // every NCCL operation of this rank is issued here
+    cudaStream_t xs = nullptr; // EX_DMA: the peer copies
+    cudaEvent_t ev_cp = nullptr;
     cudaEvent_t ev_lde[MAX_ROUNDS] = {}, ev_bar[MAX_ROUNDS] = {}, ev_unp[MAX_ROUNDS] = {}, ev_a = nullptr, ev_b = nullptr;
     u64 *flag = nullptr;                                   // barrier word
     u64 *rows = nullptr;                                   // this rank's row shard of the extended trace, R x ncols
@@ -175,6 +197,8 @@ static int dist_create(Ctx &C, int rank, int world, ncclComm_t comm, bool single
     D->comm = comm;
     D->single_process = single;
     ZK_CUDA(cudaStreamCreateWithFlags(&D->cs, cudaStreamNonBlocking));
+    ZK_CUDA(cudaStreamCreateWithFlags(&D->xs, cudaStreamNonBlocking));
+    ZK_CUDA(cudaEventCreateWithFlags(&D->ev_cp, cudaEventDisableTiming));
     for (int i = 0; i < MAX_ROUNDS; i++)
     {
         ZK_CUDA(cudaEventCreateWithFlags(&D->ev_lde[i], cudaEventDisableTiming));
@@ -223,8 +247,15 @@ static int make_plan(Plan &pl, u64 ncols, int world, bool host_input)
     const u64 blocks = (ncols + 7) / 8;
     u64 per_round[MAX_ROUNDS];
     int nr = 0;
-    if (!host_input || blocks == 0)
+    if (blocks == 0 || (!host_input && g_exchange == EX_STORES))
         per_round[nr++] = blocks;
+    else if (!host_input)
+    {
+        // staged exchange (copy engines or NCCL): three rounds so that the transfer of one hides under the next one's transform
+        // and the previous one's sponge
+        const u64 k = blocks >= 3 * (u64)world ? 3 : 1;
+        for (u64 i = 0; i < k; i++) per_round[nr++] = blocks / k + (i < blocks % k ? 1 : 0);
+    }
     else
     {
         u64 left = blocks;
@@ -283,7 +314,7 @@ static int subtree_levels(u64 leaves, u64 *off, u64 *cnt)
 // same shape.  grp != nullptr: ranks are threads of this process.
 static int dist_setup_rows(Ctx &C, Dist &D, u64 need_words)
 {
-    static const bool force_nccl = []() { const char *e = getenv("ZKGPU_EXCHANGE"); return e && !strcmp(e, "nccl"); }();
+    const bool force_nccl = exchange_wanted() == EX_NCCL;
     if (D.rows && need_words <= D.rows_cap && D.p2p_tried) return 0;
     ZK_CUDA(cudaStreamSynchronize(C.cur));
     ZK_CUDA(cudaStreamSynchronize(D.cs));
@@ -353,11 +384,13 @@ static int dist_setup_rows(Ctx &C, Dist &D, u64 need_words)
     }
     D.p2p = ok;
     D.p2p_tried = true;
+    g_exchange = ok ? exchange_wanted() : (int)EX_NCCL; // the same on every rank: `ok` was agreed on above
     u64 tab[MAX_WORLD] = {};
     for (int g = 0; g < D.world; g++) tab[g] = (u64)(uintptr_t)D.peer_rows[g];
     ZK_CUDA(cudaMemcpy(D.peer_tab, tab, sizeof(u64) * D.world, cudaMemcpyHostToDevice));
     if (getenv("ZKGPU_DIST_TRACE")) fprintf(stderr, "[zkgpu dist] rank %d/%d: row shard %llu MiB, exchange = %s\n", D.rank, D.world,
-                                            (unsigned long long)(need_words >> 17), ok ? "peer stores (fused into the LDE)" : "ncclSend/ncclRecv");
+                                            (unsigned long long)(need_words >> 17),
+                                            g_exchange == EX_STORES ? "peer stores (fused into the LDE)" : g_exchange == EX_DMA ? "copy engines (peer cudaMemcpy2DAsync)" : "ncclSend/ncclRecv");
     return 0;
 }
 
@@ -402,11 +435,11 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         set_error("zkgpu dist: N_Extended = %llu must be a multiple of the number of GPUs (%d)", (unsigned long long)n_ext, G);
         return -1;
     }
-    Plan pl;
-    ZK_TRY(make_plan(pl, ncols, G, host_input));
     cudaStream_t st = C.cur;
     ZK_TRY(ctx_pipe_streams(C));
-    ZK_TRY(dist_setup_rows(C, D, R * ncols));
+    ZK_TRY(dist_setup_rows(C, D, R * ncols)); // also settles the exchange mode, which the plan depends on
+    Plan pl;
+    ZK_TRY(make_plan(pl, ncols, G, host_input));
     D.rows_n = R;
     D.rows_c = ncols;
     const u64 sub_words = (2 * R - 1) * 4;
@@ -419,11 +452,9 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
     }
     ZK_TRY(ctx_ensure_scratch(C, 2 * n * (wmax ? wmax : 1)));
     if (host_input) ZK_TRY(dev_realloc(&D.in_buf, &D.in_cap, 2 * n * wmax));
-    if (!D.p2p)
-    {
-        ZK_TRY(dev_realloc(&D.ext_buf, &D.ext_cap, 2 * n_ext * wmax));
-        ZK_TRY(dev_realloc(&D.recv_buf, &D.recv_cap, 2 * R * rwmax));
-    }
+    const int ex = g_exchange;
+    if (ex != EX_STORES) ZK_TRY(dev_realloc(&D.ext_buf, &D.ext_cap, 2 * n_ext * wmax));
+    if (ex == EX_NCCL) ZK_TRY(dev_realloc(&D.recv_buf, &D.recv_cap, 2 * R * rwmax));
     const bool tree_is_dev = tree != nullptr && is_device_ptr(tree);
     u64 *tree_d = tree_is_dev ? tree : nullptr; // rank 0's device image of the whole tree, when there is one
     if (me == 0 && gather && !tree_is_dev)
@@ -464,7 +495,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
     };
     auto absorb_round = [&](int k) -> int {
         ZK_CUDA(cudaStreamWaitEvent(st, D.ev_bar[k], 0));
-        if (!D.p2p)
+        if (ex == EX_NCCL)
         {
             const u64 *rb = D.recv_buf + (size_t)(k & 1) * R * rwmax;
             for (int g = 0; g < G; g++)
@@ -524,10 +555,10 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         int e0, e1;
         mark("lde+", k, st);
         ZK_TRY(ctx_pipe_event(C, &e0, st));
-        u64 *ext = D.p2p ? nullptr : D.ext_buf + (size_t)b * n_ext * wmax;
+        u64 *ext = ex == EX_STORES ? nullptr : D.ext_buf + (size_t)b * n_ext * wmax;
         if (w)
         {
-            if (D.p2p)
+            if (ex == EX_STORES)
             {
                 Scatter sc;
                 sc.peer_tab = D.peer_tab;
@@ -545,9 +576,25 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         if (host_input) ZK_CUDA(cudaEventRecord(C.in_free[b], st));
         // exchange point of round k
         ZK_CUDA(cudaEventRecord(D.ev_lde[k], st));
-        ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_lde[k], 0));
-        if (D.p2p)
-            ZK_NCCL(g_nccl.AllReduce(D.flag, D.flag + 1, 1, ncclUint64, ncclSum, D.comm, D.cs)); // all stores of round k have landed
+        if (ex == EX_DMA)
+        {
+            // the copy engines carry block h (rows of rank h, contiguous in the staging buffer) into rank h's shard, at this
+            // piece's columns; the barrier below is entered once MY copies are done and left once EVERYBODY's are
+            ZK_CUDA(cudaStreamWaitEvent(D.xs, D.ev_lde[k], 0));
+            if (w)
+                for (int i = 0; i < G; i++)
+                {
+                    const int h = (me + i) % G; // start with my own rows, spread the peers
+                    ZK_CUDA(cudaMemcpy2DAsync(D.peer_rows[h] + pl.c0[k][me], ncols * sizeof(u64), ext + (size_t)h * R * w, w * sizeof(u64),
+                                              w * sizeof(u64), R, cudaMemcpyDeviceToDevice, D.xs));
+                }
+            ZK_CUDA(cudaEventRecord(D.ev_cp, D.xs));
+            ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_cp, 0));
+        }
+        else
+            ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_lde[k], 0));
+        if (ex != EX_NCCL)
+            ZK_NCCL(g_nccl.AllReduce(D.flag, D.flag + 1, 1, ncclUint64, ncclSum, D.comm, D.cs)); // all rows of round k have landed
         else
         {
             if (k >= 2) ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_unp[k - 2], 0)); // the receive slot has been unpacked
@@ -721,7 +768,8 @@ int zkgpu_dist_init(const void *nccl_unique_id, int rank, int world)
     memcpy(&id, nccl_unique_id, sizeof(id));
     ncclComm_t comm = nullptr;
     ZK_NCCL(g_nccl.CommInitRank(&comm, world, id, rank));
-    return dist_create(C, rank, world, comm, false);
+    ZK_TRY(dist_create(C, rank, world, comm, false));
+    return dist_setup_rows(C, *C.dist, 1); // collective: finds out whether the peers' memory can be mapped (exchange mode)
 }
 
 int zkgpu_init_multi(int ngpu)
@@ -768,6 +816,17 @@ int zkgpu_init_multi(int ngpu)
         ZK_TRY(dist_create(*en.c, g, ngpu, comms[g], true));
     }
     g_group.n = ngpu;
+    {
+        bool ok = exchange_wanted() != EX_NCCL;
+        for (int g = 0; g < ngpu && ok; g++)
+            for (int h = 0; h < ngpu && ok; h++)
+                if (g != h)
+                {
+                    int can = 0;
+                    if (cudaDeviceCanAccessPeer(&can, g, h) != cudaSuccess || !can) ok = false;
+                }
+        g_exchange = ok ? exchange_wanted() : (int)EX_NCCL;
+    }
     zk::Enter back(0); // the calling thread stays bound to device 0
     return back.rc;
 }
@@ -777,7 +836,7 @@ int zkgpu_dist_info(int *rank, int *world, int *peer_stores)
     ZK_ENTER;
     if (rank) *rank = C.dist ? C.dist->rank : 0;
     if (world) *world = g_group.n ? g_group.n : (C.dist ? C.dist->world : 1);
-    if (peer_stores) *peer_stores = C.dist ? (C.dist->p2p ? 1 : 0) : 0;
+    if (peer_stores) *peer_stores = C.dist ? (g_exchange == EX_STORES ? 1 : g_exchange == EX_DMA ? 2 : 0) : 0;
     return 0;
 }
 

@@ -99,6 +99,7 @@ struct Enter
     (void)C
 
 // ---- occupancy knobs of the overlapped commit pipeline (set by api.cu around its launches; zkgpu_tune for experiments)
+extern int g_coop_max_parents;      // tree levels up to this many parents: cooperative (16 lanes per hash) kernel
 extern int g_absorb_threads;         // 128 (fill the SM) or 512 (one CTA per SM)
 extern int g_ntt_threads_per_sm_cap; // 0 = fill the SM
 

@@ -362,8 +362,12 @@ class CDist:
         self.zk._check(self.zk.lib().zkgpu_dist_rows(ct.byref(p), ct.byref(r), ct.byref(c), ct.byref(sub)))
         return p.value, r.value, c.value, sub.value
 
-    def peer_stores(self):
+    def exchange(self):
+        """'stores' (peer stores fused into the LDE's last pass), 'dma' (copy engines) or 'nccl' (ncclSend/ncclRecv)."""
         ct = self.ct
         a, b, c = ct.c_int(), ct.c_int(), ct.c_int()
         self.zk._check(self.zk.lib().zkgpu_dist_info(ct.byref(a), ct.byref(b), ct.byref(c)))
-        return bool(c.value)
+        return {1: "stores", 2: "dma"}.get(c.value, "nccl")
+
+    def peer_stores(self):
+        return self.exchange() == "stores"
