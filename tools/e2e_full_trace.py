@@ -1,0 +1,53 @@
+#!/usr/bin/env python3
+"""Timeline of one all-host commit (pinned trace in, pinned extended trace + tree out; ZKGPU_PIPE_TRACE=1): where the
+2^23 x 665 call spends its PCIe time.  Also times the unchanged call pair extendPol + merkelize (commit cache).
+Run on the GPU box: python tools/e2e_full_trace.py 2> gpurun_out/e2e_full_trace.txt"""
+import ctypes, os, sys, time, torch
+os.environ["ZKGPU_PIPE_TRACE"] = "1"
+sys.path.insert(0, ".")
+import zkevm_prover_b200 as zk
+
+log_n, c = int(os.environ.get("LOGN", "23")), 665
+n, n_ext = 1 << log_n, 2 << log_n
+zk.init(0)
+zk.set_stream(torch.cuda.current_stream().cuda_stream)
+
+
+def pinned(words):
+    p = ctypes.c_void_p()
+    zk._check(zk.lib().zkgpu_malloc_host(ctypes.byref(p), words * 8))
+    return p.value
+
+
+h_in, h_ext, h_tree = pinned(n * c), pinned(n_ext * c), pinned((2 * n_ext - 1) * 4)
+d = torch.empty(n * 64, dtype=torch.int64, device="cuda")
+for k in range(0, n * c, n * 64):
+    m = min(n * 64, n * c - k)
+    zk.fill(d, m, 1, k)
+    zk.sync()
+    zk._check(zk.lib().zkgpu_memcpy(h_in + 8 * k, d.data_ptr(), 8 * m))
+del d
+torch.cuda.empty_cache()
+ntt = zk.NTT_Goldilocks(n)
+for rep in range(2):
+    t = time.perf_counter()
+    zk.extend_and_merkelize(ntt, h_ext, h_tree, h_in, n_ext, n, c)
+    print("fused all-host call %d: %.1f ms wall" % (rep, (time.perf_counter() - t) * 1e3), file=sys.stderr, flush=True)
+root = (ctypes.c_uint64 * 4).from_address(h_tree + 8 * ((2 * n_ext - 1) * 4 - 4))
+want = list(root)
+for rep in range(2):
+    t = time.perf_counter()
+    ntt.extendPol(h_ext, h_in, n_ext, n, c)
+    t1 = time.perf_counter()
+    zk.PoseidonGoldilocks.merkletree(h_tree, h_ext, c, n_ext)
+    t2 = time.perf_counter()
+    print("unchanged pair %d: extendPol %.1f ms + merkelize %.1f ms (root %s)" % (rep, (t1 - t) * 1e3, (t2 - t1) * 1e3, "ok" if list(root) == want else "DIFFERS"),
+          file=sys.stderr, flush=True)
+zk._check(zk.lib().zkgpu_tune(2, 0))
+t = time.perf_counter()
+ntt.extendPol(h_ext, h_in, n_ext, n, c)
+t1 = time.perf_counter()
+zk.PoseidonGoldilocks.merkletree(h_tree, h_ext, c, n_ext)
+t2 = time.perf_counter()
+print("pair with the commit cache OFF: extendPol %.1f ms + merkelize %.1f ms (root %s)" % ((t1 - t) * 1e3, (t2 - t1) * 1e3, "ok" if list(root) == want else "DIFFERS"),
+      file=sys.stderr, flush=True)

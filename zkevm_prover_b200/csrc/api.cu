@@ -275,7 +275,7 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
     auto strip_cols = [&](u64 s) { return start[s + 1] - start[s]; };
     // ZKGPU_PIPE_TRACE=1: print the timeline of the copies and kernels of this call (development aid; synchronises)
     static const bool trace = getenv("ZKGPU_PIPE_TRACE") != nullptr;
-    std::vector<std::pair<int, int>> h2d_ev;
+    std::vector<std::pair<int, int>> h2d_ev, d2h_ev;
     int t_origin = -1;
     if (trace) ZK_TRY(ctx_pipe_event(C, &t_origin, st));
     auto issue_h2d = [&](u64 s) -> int {
@@ -338,8 +338,12 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
         {
             ZK_CUDA(cudaEventRecord(C.out_ready[b], st));
             ZK_CUDA(cudaStreamWaitEvent(C.d2h, C.out_ready[b], 0));
+            int t0 = -1, t1 = -1;
+            if (trace) ZK_TRY(ctx_pipe_event(C, &t0, C.d2h));
             ZK_CUDA(cudaMemcpy2DAsync(out_ext + c0, ncols * sizeof(u64), out_buf[b], cw * sizeof(u64), cw * sizeof(u64), n_ext,
                                       cudaMemcpyDeviceToHost, C.d2h));
+            if (trace) ZK_TRY(ctx_pipe_event(C, &t1, C.d2h));
+            if (trace) d2h_ev.push_back({t0, t1});
             ZK_CUDA(cudaEventRecord(C.out_free[b], C.d2h));
         }
     }
@@ -353,19 +357,22 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
     {
         ZK_CUDA(cudaStreamSynchronize(st));
         if (C.h2d) ZK_CUDA(cudaStreamSynchronize(C.h2d));
+        if (C.d2h) ZK_CUDA(cudaStreamSynchronize(C.d2h));
         auto at = [&](int e) {
             float ms = 0;
             cudaEventElapsedTime(&ms, C.pool[t_origin], C.pool[e]);
             return ms;
         };
-        fprintf(stderr, "[zkgpu pipe] strip cols | h2d begin..end | lde begin..end | absorb end   (ms from call start)\n");
+        fprintf(stderr, "[zkgpu pipe] strip cols | h2d begin..end | lde begin..end | absorb end | d2h begin..end   (ms from call start)\n");
         for (u64 s = 0; s < nstrips; s++)
         {
             const auto &l = C.segs[2 * s], &a = C.segs[2 * s + 1];
             float hb = -1, he = -1;
             if (s < h2d_ev.size()) hb = at(h2d_ev[s].first), he = at(h2d_ev[s].second);
-            fprintf(stderr, "[zkgpu pipe] %2llu %4llu | %8.1f %8.1f | %8.1f %8.1f | %8.1f\n", (unsigned long long)s,
-                    (unsigned long long)strip_cols(s), hb, he, at(l.a), at(l.b), at(a.b));
+            float db = -1, de = -1;
+            if (s < d2h_ev.size()) db = at(d2h_ev[s].first), de = at(d2h_ev[s].second);
+            fprintf(stderr, "[zkgpu pipe] %2llu %4llu | %8.1f %8.1f | %8.1f %8.1f | %8.1f | %8.1f %8.1f\n", (unsigned long long)s,
+                    (unsigned long long)strip_cols(s), hb, he, at(l.a), at(l.b), at(a.b), db, de);
         }
     }
     return 0;
