@@ -438,13 +438,19 @@ def run_ours(args):
     # per step, i.e. summed over the strips; one launch per step on each rank in the multi-GPU path)
     leaf_ms = stages.get("leaves")
     leaf_bytes = (8 * c * n_ext + 32 * n_ext) / world  # reads its rows of the extended trace once, writes 4-word digests
-    traffic = None
+    traffic, traffic_note = None, None
     tp = ROOT / "profiles" / "traffic.json"
     if tp.exists():
-        traffic = json.loads(tp.read_text()).get("absorb_kernel@%dx%d/%d" % (args.log_rows, c, world))
+        tj = json.loads(tp.read_text())
+        traffic = tj.get("absorb_kernel@%dx%d/%d" % (args.log_rows, c, world))
+        traffic_note = "ncu --set full capture (profiles/), dram__bytes_read.sum + dram__bytes_write.sum summed over the step's launches"
+        if traffic is None and tj.get("absorb_kernel@%dx%d/1" % (args.log_rows, c)) is not None:
+            # the same kernel over 1/world of the rows per rank: the 1-GPU capture scaled, not a capture of this run
+            traffic = tj["absorb_kernel@%dx%d/1" % (args.log_rows, c)] / world
+            traffic_note = "1-GPU ncu capture / %d (each rank runs the same kernel over 1/%d of the rows)" % (world, world)
     achieved = leaf_bytes / (leaf_ms * 1e-3) / 1e9 if leaf_ms else None
     roofline = {"kernel": "zk::absorb_kernel (Poseidon row sponge, per step = all strips)" if world == 1 else "zk::leaves_kernel (Poseidon row sponge)", "bound": "hbm", "achieved": achieved, "peak": peak_gbs,
-                "unit": "GB/s", "frac": achieved / peak_gbs if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                "unit": "GB/s", "frac": achieved / peak_gbs if achieved else None, "traffic": traffic, "traffic_source": traffic_note, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": leaf_bytes,
                 "permutations_per_s": (n_ext * (-(-c // 8)) / world) / (leaf_ms * 1e-3) if leaf_ms else None,
                 "note": "arithmetic-bound kernel (about 1.4e9 Poseidon permutations per step: 472 64-bit modular multiplies on the "
@@ -470,6 +476,18 @@ def run_ours(args):
     roofline_lde = {"stage": "extendPol (INTT + coset NTTs, all passes)", "bound": "hbm",
                     "achieved": lde_bytes / (lde_ms * 1e-3) / 1e9 if lde_ms else None, "peak": peak_gbs, "unit": "GB/s",
                     "frac": lde_bytes / (lde_ms * 1e-3) / 1e9 / peak_gbs if lde_ms else None, "algorithmic_bytes": lde_bytes}
+    # the transform against the pipe that binds it: ncu (profiles/r1_ncu_full_2p20x665_v3.csv) has 154
+    # thread-instructions per element and 8-stage pass, ALU pipe 66-71 % of its peak at 63-65 % issue-slot utilisation, i.e. 53 %
+    # of the instructions are ALU-pipe instructions = 82 per element-pass; one cell costs 3 + 2*3 = 9 element-passes at blowup 2.
+    # ALU pipe peak: 16 lanes per SM sub-partition = 64 thread-instructions per clock per SM (tools/int_bench.cu, IADD3 class).
+    if lde_ms and args.log_blowup == 1:
+        alu_per_cell = 82.0 * 9 * (-(-args.log_rows // 8)) / 3.0
+        sm_clock = float(clocks["sm_mhz"]) * 1e6 if clocks and clocks.get("sm_mhz") else 1.965e9
+        alu_peak = 148 * 64 * sm_clock
+        alu_rate = cells / world * alu_per_cell / (lde_ms * 1e-3)
+        roofline_lde["arithmetic"] = {"bound": "ALU pipe (IADD3/LOP3/SHF/SEL)", "alu_instructions_per_cell": alu_per_cell, "achieved": alu_rate,
+                                      "peak": alu_peak, "unit": "ALU thread-instructions/s per GPU", "frac": alu_rate / alu_peak,
+                                      "source": "instruction counts from the committed ncu capture, rate measured in this run"}
 
     cpu = None
     if not args.no_cpu and world == 1:

@@ -187,8 +187,8 @@ int zkgpu_copy_block(uint64_t *dst, uint64_t dst_ld, const uint64_t *src, uint64
  *     level-major node array; other ranks pass NULL.  gather_tree == 0: the tree stays sharded.
  *     After the call zkgpu_dist_rows gives this rank's row shard of the extended trace (rows [rank*R, (rank+1)*R), R = NExt /
  *     world, row-major with ncols columns: the layout MerkleTreeGL::source has) and its subtree ((2R-1)*4 words).
- * The column-shard -> row-shard exchange is done by the LDE's own stores into the peers' row shards over NVLink (peer
- * access / CUDA IPC); ZKGPU_EXCHANGE=dma stages the rows locally and lets the copy engines push them to the peers; without
+ * The column-shard -> row-shard exchange goes into the peers' row shards over NVLink (peer
+ * access / CUDA IPC); by default the rows are staged locally and the copy engines push them to the peers (ZKGPU_EXCHANGE=stores: the LDE stores them itself); without
  * peer access, or with ZKGPU_EXCHANGE=nccl, grouped ncclSend/ncclRecv per round do it. */
 int zkgpu_init_multi(int ngpu);
 int zkgpu_nccl_unique_id(void *out128);

@@ -76,14 +76,14 @@ def main():
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
         s.close()
-        mp.spawn(spawn_rank, args=(world, log_n, c, log_b, port, "host" in extra, "nccl" if "nccl" in extra else "dma" if "dma" in extra else ""),
+        mp.spawn(spawn_rank, args=(world, log_n, c, log_b, port, "host" in extra, "nccl" if "nccl" in extra else "stores" if "stores" in extra else ""),
                  nprocs=world, join=True)
         print("dist spawn: ok")
     elif mode == "multi":
         if "nccl" in extra:
             os.environ["ZKGPU_EXCHANGE"] = "nccl"
-        if "dma" in extra:
-            os.environ["ZKGPU_EXCHANGE"] = "dma"
+        if "stores" in extra:
+            os.environ["ZKGPU_EXCHANGE"] = "stores"
         import torch  # before the library maps an NCCL: torch's own libnccl.so.2 must be the one this process holds
         import zkevm_prover_b200 as zk
         from oracle_lib import Oracle

@@ -30,12 +30,13 @@ def run(*args):
 
 
 @pytest.mark.parametrize("mode,log_n,c,log_b,extra", [
-    ("spawn", 16, 665, 1, ""),        # the headline width, device-resident pieces, peer stores fused into the LDE
+    ("spawn", 16, 665, 1, ""),        # the headline width, device-resident pieces, copy-engine exchange (the default)
+    ("spawn", 16, 665, 1, "stores"),  # peer stores fused into the LDE's last pass: one round, no staging
     ("spawn", 12, 45, 2, "host"),     # pinned host pieces: ramped rounds, blowup 4
     ("spawn", 12, 9, 1, "nccl"),      # the ncclSend/ncclRecv fallback exchange, narrow pieces
-    ("spawn", 14, 100, 1, "dma"),     # staged exchange by the copy engines, three rounds
-    ("spawn", 12, 45, 2, "dma host"),
-    ("multi", 13, 77, 1, "dma"),
+    ("spawn", 14, 100, 1, "stores"),
+    ("spawn", 12, 45, 2, "stores host"),
+    ("multi", 13, 77, 1, "stores"),
     ("multi", 16, 665, 1, ""),        # single process, host trace in, host extended trace + tree out
     ("multi", 10, 3, 3, ""),          # rows of <= 4 words are copied, not hashed; blowup 8
     ("multi", 12, 100, 1, "nccl"),
@@ -45,11 +46,12 @@ def test_two_gpus_match_one_gpu(mode, log_n, c, log_b, extra):
         pytest.skip("needs 2 GPUs")
     out = run(mode, 2, log_n, c, log_b, extra)
     if mode == "spawn":
-        assert "exchange=" + ("nccl" if "nccl" in extra else "dma" if "dma" in extra else "") in out
+        assert "exchange=" + ("nccl" if "nccl" in extra else "stores" if "stores" in extra else "dma") in out
 
 
 def test_eight_gpus_match_one_gpu():
     if ngpu() < 8:
         pytest.skip("needs 8 GPUs")
     run("spawn", 8, 14, 665, 1, "")
+    run("spawn", 8, 14, 665, 1, "stores")
     run("multi", 8, 14, 665, 1, "")

@@ -102,15 +102,18 @@ static const int MAX_WORLD = 16, MAX_ROUNDS = 16;
 //   EX_DMA     the transform writes a local staging buffer and the copy engines push the row blocks to the peers
 //              (cudaMemcpy2DAsync device-to-device over NVLink) while the SMs extend the next round / hash the previous one;
 //   EX_NCCL    grouped ncclSend/ncclRecv per round into a receive buffer that is then unpacked (no peer access needed).
-// ZKGPU_EXCHANGE=stores|dma|nccl picks one; default stores when every pair of GPUs has peer access, else nccl.
+// ZKGPU_EXCHANGE=stores|dma|nccl picks one; default dma when every pair of GPUs has peer access, else nccl.
+// Measured at H (profiles/r2_bench_n{2,8}_exchange_*.json): 2 GPUs stores 703.8 / dma 703.0 / nccl 718.5 ms per commit;
+// 8 GPUs stores 190.3 (the two scatter passes of every LDE run at the remote-store rate, 350 GB/s per GPU: LDE 64.0 ms
+// instead of 46.6) / dma 174.6 (LDE 48.7, nothing exposed).
 enum { EX_STORES = 0, EX_DMA = 1, EX_NCCL = 2 };
 static int exchange_wanted()
 {
     static const int w = []() {
         const char *e = getenv("ZKGPU_EXCHANGE");
         if (e && !strcmp(e, "nccl")) return (int)EX_NCCL;
-        if (e && !strcmp(e, "dma")) return (int)EX_DMA;
-        return (int)EX_STORES;
+        if (e && !strcmp(e, "stores")) return (int)EX_STORES;
+        return (int)EX_DMA;
     }();
     return w;
 }
@@ -196,8 +199,14 @@ static int dist_create(Ctx &C, int rank, int world, ncclComm_t comm, bool single
     D->world = world;
     D->comm = comm;
     D->single_process = single;
-    ZK_CUDA(cudaStreamCreateWithFlags(&D->cs, cudaStreamNonBlocking));
-    ZK_CUDA(cudaStreamCreateWithFlags(&D->xs, cudaStreamNonBlocking));
+    // The exchange streams get the highest priority: a strided device-to-device copy and NCCL's barrier are kernels too, and
+    // at equal priority the block scheduler would only start them once the sponge kernel queued before them has dispatched
+    // its last CTA (measured at 8 GPUs, profiles/r2_dist_timeline_n8_dma.txt: every round's barrier arrived ~10 ms AFTER the
+    // previous round's sponge had finished instead of during it).
+    int prio_lo = 0, prio_hi = 0;
+    ZK_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    ZK_CUDA(cudaStreamCreateWithPriority(&D->cs, cudaStreamNonBlocking, prio_hi));
+    ZK_CUDA(cudaStreamCreateWithPriority(&D->xs, cudaStreamNonBlocking, prio_hi));
     ZK_CUDA(cudaEventCreateWithFlags(&D->ev_cp, cudaEventDisableTiming));
     for (int i = 0; i < MAX_ROUNDS; i++)
     {
@@ -251,9 +260,10 @@ static int make_plan(Plan &pl, u64 ncols, int world, bool host_input)
         per_round[nr++] = blocks;
     else if (!host_input)
     {
-        // staged exchange (copy engines or NCCL): three rounds so that the transfer of one hides under the next one's transform
+        // staged exchange (copy engines or NCCL): two rounds so that the transfer of one hides under the next one's transform
         // and the previous one's sponge
-        const u64 k = blocks >= 3 * (u64)world ? 3 : 1;
+        static const u64 want = []() { const char *e = getenv("ZKGPU_DMA_ROUNDS"); return (u64)(e && atoi(e) > 0 && atoi(e) <= MAX_ROUNDS ? atoi(e) : 2); }();
+        const u64 k = blocks >= want * (u64)world ? want : 1; // (8 GPUs, H: 2 rounds 184.7 ms, 3 rounds 185.9, 5 rounds 193.3)
         for (u64 i = 0; i < k; i++) per_round[nr++] = blocks / k + (i < blocks % k ? 1 : 0);
     }
     else
@@ -623,22 +633,16 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         C.segs.push_back({1, e0, e1});
     }
     ZK_CUDA(cudaEventRecord(C.ev[2], st));
-    ZK_TRY(merkle_levels(D.sub, R, st));
-
-    // ---- stitch: level l of the global tree = the ranks' slices side by side (l <= log2 R), then the top over the sub-roots
+    // ---- stitch: level l of the global tree = the ranks' slices side by side (l <= log2 R), then the top over the sub-roots.
+    // The leaf level is half of all the bytes: it travels to rank 0 while the node levels are being hashed.
     u64 soff[40], scnt[40], goff[40], gcnt[40];
     const int sl = subtree_levels(R, soff, scnt);
     subtree_levels(n_ext, goff, gcnt);
     const int LR = sl - 1; // level of the sub-roots
-    ZK_CUDA(cudaEventRecord(D.ev_a, st));
-    ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_a, 0));
-    u64 *top_dst = (me == 0 && tree_d) ? tree_d + goff[LR] : D.top;
-    ZK_NCCL(g_nccl.AllGather(D.sub + soff[LR], top_dst, 4, ncclUint64, D.comm, D.cs));
-    if (gather)
-    {
+    auto ship_levels = [&](int l0, int l1) -> int {
         // process-per-GPU form, or a device tree on rank 0: every rank ships its level slices to rank 0
         ZK_NCCL(g_nccl.GroupStart());
-        for (int l = 0; l < LR; l++)
+        for (int l = l0; l < l1; l++)
         {
             if (me != 0)
                 ZK_NCCL(g_nccl.Send(D.sub + soff[l], scnt[l] * 4, ncclUint64, 0, D.comm, D.cs));
@@ -646,6 +650,21 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
                 for (int g = 1; g < G; g++) ZK_NCCL(g_nccl.Recv(tree_d + goff[l] + (size_t)g * scnt[l] * 4, scnt[l] * 4, ncclUint64, g, D.comm, D.cs));
         }
         ZK_NCCL(g_nccl.GroupEnd());
+        return 0;
+    };
+    if (gather && LR > 0)
+    {
+        ZK_CUDA(cudaStreamWaitEvent(D.cs, C.ev[2], 0));
+        ZK_TRY(ship_levels(0, 1));
+    }
+    ZK_TRY(merkle_levels(D.sub, R, st));
+    ZK_CUDA(cudaEventRecord(D.ev_a, st));
+    ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_a, 0));
+    u64 *top_dst = (me == 0 && tree_d) ? tree_d + goff[LR] : D.top;
+    ZK_NCCL(g_nccl.AllGather(D.sub + soff[LR], top_dst, 4, ncclUint64, D.comm, D.cs));
+    if (gather)
+    {
+        if (LR > 1) ZK_TRY(ship_levels(1, LR));
         if (me == 0)
             for (int l = 0; l < LR; l++)
                 ZK_CUDA(cudaMemcpyAsync(tree_d + goff[l], D.sub + soff[l], scnt[l] * 32, cudaMemcpyDeviceToDevice, st));

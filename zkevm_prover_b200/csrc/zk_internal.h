@@ -54,6 +54,8 @@ struct Ctx
     size_t scratch_words = 0;
     cudaEvent_t ev[8] = {};
     bool timed = false;
+    bool capturing = false; // the current stream is being captured into a CUDA graph (api.cu: commit_graph)
+    unsigned long long buffers_gen = 0; // bumped whenever scratch or a twiddle table moves: captured graphs hold their addresses
     float stage[5] = {0, 0, 0, 0, 0};
     // strip pipeline (commit_pipeline): copy streams, buffer hand-over events and per-strip timing segments
     cudaStream_t h2d = nullptr, d2h = nullptr;
