@@ -37,8 +37,7 @@ const char *zkgpu_last_error(void);
 int zkgpu_device_count(void);
 uint64_t zkgpu_launch_count(void);     /* kernels this library has launched so far in this process */
 int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes);
-/* tuning / experiment hook: key 0 = threads per CTA of the sponge kernel (128 | 512), key 2 = commit cache on/off, key 3 = largest
- * tree level (parents) hashed by the cooperative 16-lanes-per-hash kernel (0 = never), key 1 = cap on transform threads per
+/* tuning / experiment hook: key 0 = threads per CTA of the sponge kernel (128 | 512), key 2 = commit cache on/off, key 1 = cap on transform threads per
  * SM (0 = none).  Used by tools/overlap_probe.py; not needed in normal use. */
 int zkgpu_tune(int key, int value);
 /* device-memory helpers so that C/C++ hosts need no CUDA headers */

@@ -671,28 +671,3 @@ def test_commit_cache_serves_the_unchanged_call_pair():
     mt.merkelize()
     assert_eq(mt.nodes, O.merkletree(ext, c, n * b), "modified buffer")
 
-
-def test_small_commit_graph_replay():
-    """Small device-resident commits are captured into a CUDA graph on their second call and replayed afterwards
-    (csrc/api.cu: commit_graph).  Same buffers, new contents every call: call 1 is enqueued directly, call 2 is the capture,
-    calls 3-4 are replays; a big commit in between moves the library's scratch, which must invalidate the captured graph."""
-    import torch
-    for n, c, b in ((1 << 12, 8, 2), (1 << 10, 3, 4), (1 << 11, 45, 2)):
-        d_in = torch.zeros(n * c, dtype=torch.int64, device="cuda")
-        d_ext = torch.zeros(n * b * c, dtype=torch.int64, device="cuda")
-        d_tree = torch.zeros((2 * n * b - 1) * 4, dtype=torch.int64, device="cuda")
-        ntt = zk.NTT_Goldilocks(n)
-        for rep in range(6):
-            a = O.fill(n * c, SEED, 100 + rep).reshape(n, c)
-            d_in.copy_(_dev(a))
-            if rep == 4:  # grow the scratch: 2^18 x 40 needs more than anything above
-                big_in = torch.zeros((1 << 18) * 40, dtype=torch.int64, device="cuda")
-                big_ext = torch.zeros((1 << 19) * 40, dtype=torch.int64, device="cuda")
-                big_tree = torch.zeros(((1 << 20) - 1) * 4, dtype=torch.int64, device="cuda")
-                zk.extend_and_merkelize(zk.NTT_Goldilocks(1 << 18), big_ext, big_tree, big_in, 1 << 19, 1 << 18, 40)
-                del big_in, big_ext, big_tree
-            zk.extend_and_merkelize(ntt, d_ext, d_tree, d_in, n * b, n, c)
-            zk.sync()
-            want = O.extend_pol(a, n * b)
-            assert_eq(_host(d_ext), want, "ext, call %d of %r" % (rep, (n, c, b)))
-            assert_eq(_host(d_tree), O.merkletree(want, c, n * b), "tree, call %d of %r" % (rep, (n, c, b)))

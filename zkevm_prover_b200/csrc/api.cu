@@ -216,7 +216,10 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
         ZK_CUDA(cudaMemGetInfo(&free_b, &total_b));
         free_b += C.scratch_words * sizeof(u64);
         size_t budget = (size_t)(0.6 * (double)free_b);
-        const size_t cap = (size_t)24 << 30;
+        // with a device-resident extended trace most of the memory belongs to the caller: stay small.  With a host-resident
+        // one the strips are all the library holds, and wide strips are what the copies want (rows of 384 B moved at
+        // 29 GB/s up and 36 GB/s down, profiles/r2_e2e_full_trace.txt; the strided copies reach the link rate from ~900 B)
+        const size_t cap = (size_t)(out_dev ? 24 : 72) << 30;
         if (budget > cap) budget = cap;
         w = budget / (per_col * sizeof(u64));
     }
@@ -546,102 +549,6 @@ static bool cache_take(const u64 *host, u64 nrows, u64 ncols, Resident *out)
         return same;
     }
     return false;
-}
-
-// ---------------------------------------------------------------------------------------------------
-// CUDA graphs for small device-resident commits, keyed by (pointers, shape, stream).  First call with a key: enqueued
-// directly (builds twiddle tables, sizes the scratch).  Second call: the same enqueue sequence is captured and instantiated.
-// Later calls: one cudaGraphLaunch.  Anything that goes wrong during capture drops the entry and the caller enqueues
-// directly.  ZKGPU_GRAPHS=0 turns it off.
-// ---------------------------------------------------------------------------------------------------
-struct GraphEntry
-{
-    const void *out, *tree, *in;
-    unsigned log_n, log_b;
-    u64 ncols;
-    cudaStream_t st;
-    int seen;
-    cudaGraphExec_t exec;
-    unsigned long long gen; // Ctx::buffers_gen at capture time
-};
-static std::map<int, std::vector<GraphEntry>> g_graphs; // per device; guarded by the context lock
-static bool graphs_enabled()
-{
-    static const bool on = []() { const char *e = getenv("ZKGPU_GRAPHS"); return !(e && e[0] == '0'); }();
-    return on;
-}
-static int commit_enqueue_device(Ctx &C, u64 *out_ext, u64 *tree, const u64 *input, unsigned log_n, unsigned log_b, u64 ncols, cudaStream_t st)
-{
-    const u64 n_ext = (u64)1 << (log_n + log_b);
-    if (ncols <= 4)
-    {
-        ZK_TRY(lde_all(C, out_ext, ncols, input, ncols, log_n, log_b, ncols, st));
-        return merkle_all(tree, out_ext, ncols, n_ext, st, nullptr);
-    }
-    ZK_TRY(commit_pipeline(C, out_ext, true, tree, input, true, log_n, log_b, ncols, st));
-    return merkle_levels(tree, n_ext, st);
-}
-// 0: replayed (or captured and launched); 1: the caller must enqueue directly; < 0: error
-static int commit_graph(Ctx &C, u64 *out_ext, u64 *tree, const u64 *input, unsigned log_n, unsigned log_b, u64 ncols, cudaStream_t st)
-{
-    auto &vec = g_graphs[C.device];
-    GraphEntry *ge = nullptr;
-    for (auto &g : vec)
-        if (g.out == out_ext && g.tree == tree && g.in == input && g.log_n == log_n && g.log_b == log_b && g.ncols == ncols && g.st == st) ge = &g;
-    if (!ge)
-    {
-        if (vec.size() >= 16)
-        {
-            if (vec.front().exec) cudaGraphExecDestroy(vec.front().exec);
-            vec.erase(vec.begin());
-        }
-        vec.push_back({out_ext, tree, input, log_n, log_b, ncols, st, 1, nullptr, 0});
-        return 1;
-    }
-    if (ge->exec && ge->gen != C.buffers_gen)
-    {
-        cudaGraphExecDestroy(ge->exec); // the scratch or a table it points into has moved since
-        ge->exec = nullptr;
-        return 1;                       // this call enqueues directly (and re-sizes), the next one captures again
-    }
-    if (ge->exec)
-    {
-        ZK_CUDA(cudaGraphLaunch(ge->exec, st));
-        C.timed = false; // no per-stage events in a replay
-        return 0;
-    }
-    if (ge->seen < 0) return 1; // capture failed before: stay on the direct path
-    cudaGraph_t graph = nullptr;
-    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) != cudaSuccess)
-    {
-        cudaGetLastError();
-        ge->seen = -1;
-        return 1;
-    }
-    C.capturing = true;
-    const int rc = commit_enqueue_device(C, out_ext, tree, input, log_n, log_b, ncols, st);
-    C.capturing = false;
-    cudaError_t e = cudaStreamEndCapture(st, &graph);
-    if (rc < 0 || e != cudaSuccess || graph == nullptr)
-    {
-        cudaGetLastError();
-        if (graph) cudaGraphDestroy(graph);
-        ge->seen = -1;
-        return 1;
-    }
-    e = cudaGraphInstantiate(&ge->exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (e != cudaSuccess)
-    {
-        cudaGetLastError();
-        ge->exec = nullptr;
-        ge->seen = -1;
-        return 1;
-    }
-    ge->gen = C.buffers_gen;
-    ZK_CUDA(cudaGraphLaunch(ge->exec, st));
-    C.timed = false;
-    return 0;
 }
 
 // "device pointers only" entry points: reject host pointers and mis-aligned digest arrays (the kernels access leaves and
@@ -1355,13 +1262,6 @@ int zkgpu_extend_and_merkelize(void *, uint64_t *out_ext, uint64_t *tree, const 
         return -1;
     }
     const u64 tree_words = (2 * n_ext - 1) * 4;
-    // Small device-resident commits are bound by launch gaps (2^16 x 8: ~25 launches of a few microseconds each): the
-    // second call with the same arguments is captured into a CUDA graph and every later one replays it.
-    if (in_dev && out_dev && tree_dev && ncols > 0 && n_ext * ncols <= ((u64)1 << 24) && graphs_enabled())
-    {
-        int rc = commit_graph(C, out_ext, tree, input, log_n, log_b, ncols, st);
-        if (rc != 1) return rc; // 1: not replayed, enqueue directly below
-    }
     u64 leaves_sent = 0;
     Staged dtree;
     u64 *d_tree = tree;
@@ -1519,7 +1419,6 @@ int zkgpu_tune(int key, int value)
     {
     case 0: g_absorb_threads = value == 512 ? 512 : 128; return 0;
     case 1: g_ntt_threads_per_sm_cap = value < 0 ? 0 : value; return 0;
-    case 3: g_coop_max_parents = value < 0 ? 0 : value; return 0; // 0: one thread per hash on every level
     case 2: g_fuse_commit = value ? 1 : 0; return 0; // commit cache: extendPol with host pointers also hashes (default on)
     }
     set_error("zkgpu_tune: unknown key %d", key);

@@ -129,7 +129,6 @@ int ctx_ensure_scratch(Ctx &C, size_t words)
         ZK_CUDA(cudaFree(C.scratch));
         C.scratch = nullptr;
         C.scratch_words = 0;
-        C.buffers_gen++;
     }
     cudaError_t e = cudaMalloc(&C.scratch, words * sizeof(u64));
     if (e != cudaSuccess)

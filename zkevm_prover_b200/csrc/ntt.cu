@@ -365,7 +365,6 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
                 cudaFree(kv.second.second);
             }
             C.tabs.clear();
-            C.buffers_gen++;
         }
         const u32 n1 = log_n > 12 ? (1u << (log_n - 12)) : 1u;
         u64 *d0 = nullptr, *d1 = nullptr;
@@ -378,7 +377,7 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
         ZK_CUDA(cudaEventRecord(C.tab_ev, st));
         it = C.tabs.emplace(key, std::make_pair(d0, d1)).first;
     }
-    else if (!C.capturing) // a graph under capture must not depend on an event recorded outside it; its tables are long built
+    else
         ZK_CUDA(cudaStreamWaitEvent(st, C.tab_ev, 0));
     *G0 = it->second.first;
     *G1 = it->second.second;

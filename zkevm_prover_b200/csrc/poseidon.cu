@@ -708,103 +708,6 @@ __global__ void __launch_bounds__(128) level_kernel(u64 *parents, const u64 *chi
 }
 
 
-// ---------------------------------------------------------------------------------------------------
-// Cooperative permutation for SMALL tree levels.  One thread per hash takes ~16 k dependent-ish instructions, about 25 us,
-// whatever the level size: the top of every tree (and all of a small tree) is bound by that latency, not by throughput
-// (profiles/r1_small_shape_coop_levels.txt: 17 launches x 27 us of a 0.67 ms commit at 2^16 x 8).  Here 16 lanes share one
-// state — lane i < 12 holds word i — so the S-box layer of a full round is one x^7 per lane and the MDS product is 12
-// shuffles and 24 small-constant IMAD.WIDE per lane: ~5 k instructions on the critical path instead of 16 k.  It costs
-// ~5x more instructions per hash in total, so merkle_levels uses it only where a level cannot fill the GPU anyway.
-// Dense form of the permutation, as poseidon_permute_state (same words out).
-// ---------------------------------------------------------------------------------------------------
-__constant__ u32 c_circ[12] = {17, 20, 34, 18, 39, 13, 13, 28, 2, 16, 41, 15}; // M[0][i] without the +8 at [0][0]
-
-struct CoopLane
-{
-    int lane;    // 0..15, words live in lanes 0..11
-    u32 m[12];   // m[j] = M[j][lane] without the diagonal term = circ[(lane - j) mod 12]
-};
-__device__ __forceinline__ void coop_init(CoopLane &L, int lane)
-{
-    L.lane = lane;
-#pragma unroll
-    for (int j = 0; j < 12; j++) L.m[j] = c_circ[(lane - j + 24) % 12];
-}
-// x <- (M x)[lane]: every lane gathers the twelve words with shuffles inside its 16-lane group
-__device__ __forceinline__ u64 coop_mds(const CoopLane &L, u64 x)
-{
-    const u32 xl = (u32)x, xh = (u32)(x >> 32);
-    u64 al = 0, ah = 0;
-#pragma unroll
-    for (int j = 0; j < 12; j++)
-    {
-        const u32 l = __shfl_sync(0xFFFFFFFFu, xl, j, 16), h = __shfl_sync(0xFFFFFFFFu, xh, j, 16);
-        al += (u64)l * L.m[j];
-        ah += (u64)h * L.m[j];
-    }
-    if (L.lane == 0)
-    {
-        al += (u64)xl * 8u;
-        ah += (u64)xh * 8u;
-    }
-    return mds_combine(al, ah); // al, ah < 2^42
-}
-// state word `lane` of hash_full_result(state); lanes 12..15 compute on zeros and are ignored
-__device__ __forceinline__ u64 coop_permute(const CoopLane &L, u64 x)
-{
-    const int i = L.lane < 12 ? L.lane : 0;
-    x = gl::add(x, c_C[i]);
-#pragma unroll 1
-    for (int r = 0; r < 4; r++)
-    {
-        x = pow7_add(x, c_RC[r * 12 + i]);
-        x = coop_mds(L, x);
-    }
-#pragma unroll 1
-    for (int q = 0; q < 22; q++)
-    {
-        if (L.lane == 0) x = pow7_add(x, c_C[60 + q]);
-        x = coop_mds(L, x);
-    }
-#pragma unroll 1
-    for (int r = 4; r < 8; r++)
-    {
-        x = pow7_add(x, c_RC[r * 12 + i]);
-        x = coop_mds(L, x);
-    }
-    return x;
-}
-// one level, 16 lanes per parent
-__global__ void __launch_bounds__(256) coop_level_kernel(u64 *parents, const u64 *children, u64 nparents)
-{
-    CoopLane L;
-    coop_init(L, threadIdx.x & 15);
-    const u64 i = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
-    const bool live = i < nparents; // whole 16-lane groups are live or not; a warp holds two groups, shuffles stay inside a group
-    u64 x = 0;
-    if (live && L.lane < 8) x = children[i * 8 + L.lane];
-    x = coop_permute(L, x);
-    if (live && L.lane < 4) parents[i * 4 + L.lane] = gl::canon(x);
-}
-// every remaining level above `pending` (<= 64) nodes in one CTA: 64 groups of 16 lanes, a barrier between levels
-__global__ void __launch_bounds__(1024) coop_top_kernel(u64 *tree, u64 pending)
-{
-    CoopLane L;
-    coop_init(L, threadIdx.x & 15);
-    const u64 g = threadIdx.x >> 4;
-    u64 off = 0;
-    while (pending > 1)
-    {
-        const u64 n = pending >> 1;
-        u64 x = 0;
-        if (g < n && L.lane < 8) x = tree[off + g * 8 + L.lane];
-        x = coop_permute(L, x);
-        if (g < n && L.lane < 4) tree[off + pending * 4 + g * 4 + L.lane] = gl::canon(x);
-        off += pending * 4;
-        pending = n;
-        __syncthreads(); // the next level reads what this CTA just wrote
-    }
-}
 
 // ---------------------------------------------------------------------------------------------------
 // host side
@@ -913,30 +816,18 @@ int merkle_leaves_batch(u64 *leaves, const u64 *input, u64 ncols, u64 dim, u64 b
     return 0;
 }
 
-// Levels with at most this many parents use the cooperative kernel (zkgpu_tune key 3).  It spends ~86 k thread-instructions
-// per hash against ~16 k for one thread per hash, so it only wins while the level is latency-bound: measured at 2^16 x 8
-// (profiles/r2_small_shapes.txt) a threshold of 2^15 LOST 0.17 ms (level 2^15: 156 us of throughput against 27 us of
-// latency); break-even is near 6 k parents.
-int g_coop_max_parents = 1 << 12;
 int merkle_levels(u64 *tree, u64 nrows, cudaStream_t st)
 {
     ZK_TRY(poseidon_init_constants());
-    // reference loop (poseidon_goldilocks.cpp:283-300) for a power-of-two number of leaves
+    // reference loop (poseidon_goldilocks.cpp:283-300) for a power-of-two number of leaves.  Small levels are bound by the
+    // latency of ONE permutation (~27 us: 30 rounds, each an S-box chain followed by an MDS chain), not by launches: a
+    // cooperative 16-lanes-per-hash kernel measured 23-30 us per level in both rounds (profiles/r1_small_shape_coop_levels.txt,
+    // profiles/r2_small_shapes.txt) and is not kept.
     u64 pending = nrows, next_index = 0;
     while (pending > 1)
     {
         const u64 next_n = pending / 2;
-        if (pending <= 64 && g_coop_max_parents > 0)
-        {
-            coop_top_kernel<<<1, 1024, 0, st>>>(tree + next_index, pending); // all the remaining levels
-            ZK_LAUNCHED();
-            ZK_CUDA(cudaGetLastError());
-            break;
-        }
-        if (next_n <= (u64)g_coop_max_parents)
-            coop_level_kernel<<<nblocks(next_n * 16, 256), 256, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
-        else
-            level_kernel<<<nblocks(next_n, 128), 128, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
+        level_kernel<<<nblocks(next_n, 128), 128, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
         ZK_LAUNCHED();
         ZK_CUDA(cudaGetLastError());
         next_index += pending * 4;

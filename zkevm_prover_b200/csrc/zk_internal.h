@@ -54,8 +54,6 @@ struct Ctx
     size_t scratch_words = 0;
     cudaEvent_t ev[8] = {};
     bool timed = false;
-    bool capturing = false; // the current stream is being captured into a CUDA graph (api.cu: commit_graph)
-    unsigned long long buffers_gen = 0; // bumped whenever scratch or a twiddle table moves: captured graphs hold their addresses
     float stage[5] = {0, 0, 0, 0, 0};
     // strip pipeline (commit_pipeline): copy streams, buffer hand-over events and per-strip timing segments
     cudaStream_t h2d = nullptr, d2h = nullptr;
@@ -101,7 +99,6 @@ struct Enter
     (void)C
 
 // ---- occupancy knobs of the overlapped commit pipeline (set by api.cu around its launches; zkgpu_tune for experiments)
-extern int g_coop_max_parents;      // tree levels up to this many parents: cooperative (16 lanes per hash) kernel
 extern int g_absorb_threads;         // 128 (fill the SM) or 512 (one CTA per SM)
 extern int g_ntt_threads_per_sm_cap; // 0 = fill the SM
 
