@@ -149,7 +149,9 @@ def test_piece_plan():
             else:
                 assert sum(w for _, w in plan[0]) == min(16 * world, 665) or K == 1
     K, plan = dc.piece_plan(665, 8)
-    assert K == 3 and [sum(w for _, w in r) for r in plan] == [128, 256, 281]
+    assert K == 4 and [sum(w for _, w in r) for r in plan] == [128, 256, 160, 121]  # ramp up, ramp down
+    K, plan = dc.piece_plan(665, 2)
+    assert [sum(w for _, w in r) for r in plan][-2:] == [48, 25] and K == 8
     assert dc.piece_plan(665, 8, 3)[1][0][0] == (0, 28)  # explicit rounds (Python model only): equal rounds
     assert dc.piece_plan(9, 4) == (1, [[(0, 3), (3, 2), (5, 2), (7, 2)]])
     assert dc.piece_plan(0, 2) == (1, [[(0, 0), (0, 0)]])

@@ -789,12 +789,13 @@ int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_
         if (L > 8) ZK_TRY(ctx_ensure_scratch(C, words));
         return ntt_transform(dst, ncols, src, ncols, C.scratch, L, ncols, inverse != 0, pre, post, st);
     }
-    Staged d;
-    ZK_TRY(d.alloc(words));
-    if (L > 8) ZK_TRY(ctx_ensure_scratch(C, words));
-    ZK_CUDA(cudaMemcpyAsync(d.d, src, words * sizeof(u64), cudaMemcpyHostToDevice, st));
-    ZK_TRY(ntt_transform(d.d, ncols, d.d, ncols, C.scratch, L, ncols, inverse != 0, pre, post, st));
-    ZK_CUDA(cudaMemcpyAsync(dst, d.d, words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    // host pointers: the device image and the transform's scratch both live in the context's scratch area (no allocation
+    // per call: stage 4 and FRI call this in a loop, starks.cpp:262-285, friProve.cpp:100-102)
+    ZK_TRY(ctx_ensure_scratch(C, 2 * words));
+    u64 *d = C.scratch, *tmp = C.scratch + words;
+    ZK_CUDA(cudaMemcpyAsync(d, src, words * sizeof(u64), cudaMemcpyHostToDevice, st));
+    ZK_TRY(ntt_transform(d, ncols, d, ncols, tmp, L, ncols, inverse != 0, pre, post, st));
+    ZK_CUDA(cudaMemcpyAsync(dst, d, words * sizeof(u64), cudaMemcpyDeviceToHost, st));
     ZK_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
