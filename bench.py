@@ -429,6 +429,9 @@ def run_ours(args):
                            "root": " ".join("%016x" % (int(x) & (2**64 - 1)) for x in s_tree[-4:].cpu().tolist())}
             del s_in, s_ext, s_tree
 
+    exchange_mode = cd.exchange() if world > 1 else None
+    if world > 1:
+        cd.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -498,7 +501,7 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic",
             "config": {"workload": workload_name(args), "rows_log2": args.log_rows, "cols": c, "blowup": b,
-                       "parallelism": "1 gpu" if world == 1 else "C ABI zkgpu_dist_commit: column pieces LDE x%d, exchange = %s, row-sharded sponge, NCCL barriers + tree stitch" % (world, {"stores": "peer stores fused into the LDE's last pass (NVLink)", "dma": "copy engines, peer cudaMemcpy2DAsync (NVLink)", "nccl": "ncclSend/ncclRecv"}[cd.exchange()]),
+                       "parallelism": "1 gpu" if world == 1 else "C ABI zkgpu_dist_commit: column pieces LDE x%d, exchange = %s, row-sharded sponge, NCCL barriers + tree stitch" % (world, {"stores": "peer stores fused into the LDE's last pass (NVLink)", "dma": "copy engines, peer cudaMemcpy2DAsync (NVLink)", "nccl": "ncclSend/ncclRecv"}[exchange_mode]),
                        "l2": "inputs (%.1f GB) larger than L2, no flush" % (cells * 8 / 1e9)},
             "stages_ms": {"STARK_STEP_1_LDE": stages.get("lde"), "EXCHANGE": stages.get("exchange"),  # N>1: exposed wait only
                           "MERKLE_LEAVES": stages.get("leaves"), "MERKLE_NODES": stages.get("nodes"),

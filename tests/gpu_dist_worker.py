@@ -62,6 +62,7 @@ def spawn_rank(rank, world, log_n, c, log_b, port, host_input, exchange):
                 bad = np.nonzero(got != want_tree)[0]
                 assert bad.size == 0, "tree differs at %d words, first %d (rep %d)" % (bad.size, bad[0], rep)
         print("rank %d ok: exchange=%s rounds=%d" % (rank, cd.exchange(), K), flush=True)
+        cd.close()
     finally:
         dist.destroy_process_group()
 
@@ -106,7 +107,8 @@ def main():
         assert np.array_equal(dtree.cpu().numpy().view(np.uint64), want_tree), "device-0 tree differs"
         r, w, ps = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
         zk._check(zk.lib().zkgpu_dist_info(ctypes.byref(r), ctypes.byref(w), ctypes.byref(ps)))
-        print("dist multi: ok world=%d peer_stores=%d" % (w.value, ps.value))
+        zk._check(zk.lib().zkgpu_dist_finalize())
+        print("dist multi: ok world=%d exchange=%d" % (w.value, ps.value))
     else:
         raise SystemExit("unknown mode")
 

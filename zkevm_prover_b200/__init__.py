@@ -21,8 +21,11 @@ __all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "Po
            "extend_and_merkelize", "stage4_commit", "invalidate", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
 
 GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
+import os
+
 _HERE = pathlib.Path(__file__).resolve().parent
-lib_path = _HERE / "libzkgpu.so"
+# ZKGPU_LIB: an alternative build of the same library (kernel-variant experiments); the product is libzkgpu.so beside this file
+lib_path = pathlib.Path(os.environ["ZKGPU_LIB"]) if os.environ.get("ZKGPU_LIB") else _HERE / "libzkgpu.so"
 
 _u64 = ctypes.c_uint64
 _vp = ctypes.c_void_p
@@ -74,6 +77,7 @@ ABI_SYMBOLS = {
     "zkgpu_dist_info": (_int, [ctypes.POINTER(_int), ctypes.POINTER(_int), ctypes.POINTER(_int)]),
     "zkgpu_dist_plan": (_int, [_u64, _int, _int, ctypes.POINTER(_int), ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
     "zkgpu_dist_commit": (_int, [_vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_u64), _int, _int, _u64, _u64, _u64]),
+    "zkgpu_dist_finalize": (_int, []),
     "zkgpu_dist_rows": (_int, [ctypes.POINTER(_vp), ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_vp)]),
 }
 

@@ -488,10 +488,43 @@ static bool fuse_enabled()
     }
     return g_fuse_commit != 0;
 }
+// pinned tree buffers of the multi-GPU path are recycled: pinning 1 GB costs a few hundred milliseconds
+static std::mutex g_pin_mu;
+static std::vector<std::pair<u64 *, size_t>> g_pin_pool; // (buffer, words)
+static u64 *pinned_take(size_t words)
+{
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        for (size_t i = 0; i < g_pin_pool.size(); i++)
+            if (g_pin_pool[i].second >= words)
+            {
+                u64 *p = g_pin_pool[i].first;
+                g_pin_pool.erase(g_pin_pool.begin() + i);
+                return p;
+            }
+    }
+    u64 *p = nullptr;
+    if (cudaMallocHost(&p, words * sizeof(u64)) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+static void pinned_give(u64 *p, size_t words)
+{
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    if (g_pin_pool.size() >= 2)
+    {
+        cudaFreeHost(g_pin_pool.front().first);
+        g_pin_pool.erase(g_pin_pool.begin());
+    }
+    g_pin_pool.push_back({p, words});
+}
 static void cache_free(Resident &r)
 {
     if (r.d_tree) cudaFree(r.d_tree);
-    if (r.h_tree) cudaFreeHost(r.h_tree);
+    if (r.h_tree) pinned_give(r.h_tree, (2 * r.nrows - 1) * 4);
     r.d_tree = r.h_tree = nullptr;
 }
 // drop every entry whose buffer overlaps [p, p + bytes)  (bytes == 0: exact pointer; p == nullptr: everything)
@@ -926,9 +959,10 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
         r.host = output;
         r.nrows = n_ext;
         r.ncols = ncols;
-        if (cudaMallocHost(&r.h_tree, (2 * n_ext - 1) * 4 * sizeof(u64)) != cudaSuccess)
+        r.h_tree = pinned_take((2 * n_ext - 1) * 4);
+        if (!r.h_tree)
         {
-            set_error("extendPol: cannot allocate the pinned tree buffer: %s", cudaGetErrorString(cudaGetLastError()));
+            set_error("extendPol: cannot allocate the pinned tree buffer");
             return -4;
         }
         const int rc = dist_multi_commit(output, r.h_tree, input, n_ext, n, ncols);

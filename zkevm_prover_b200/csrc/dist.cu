@@ -922,6 +922,44 @@ int zkgpu_dist_commit(void *, uint64_t *tree, const uint64_t *const *pieces, con
     return dist_commit_rank(C, ps, host_input != 0, n_ext, n, ncols, tree, false, gather_tree != 0, nullptr);
 }
 
+static void dist_destroy(Ctx &C)
+{
+    Dist *D = C.dist;
+    if (!D) return;
+    cudaStreamSynchronize(C.cur);
+    cudaStreamSynchronize(D->cs);
+    cudaStreamSynchronize(D->xs);
+    if (!D->single_process)
+        for (int g = 0; g < D->world; g++)
+            if (D->ipc_open[g]) cudaIpcCloseMemHandle(D->ipc_open[g]);
+    u64 *bufs[] = {D->rows, D->sub, D->top, D->tree_dev, D->in_buf, D->ext_buf, D->recv_buf, D->ipc_scratch, D->flag, D->peer_tab};
+    for (u64 *b : bufs)
+        if (b) cudaFree(b);
+    if (D->comm) g_nccl.CommDestroy(D->comm);
+    cudaStreamDestroy(D->cs);
+    cudaStreamDestroy(D->xs);
+    delete D;
+    C.dist = nullptr;
+}
+
+int zkgpu_dist_finalize(void)
+{
+    if (g_group.n)
+    {
+        for (int g = 0; g < g_group.n; g++)
+        {
+            Enter en(g_group.ctx[g]->device);
+            if (en.rc >= 0) dist_destroy(*en.c);
+        }
+        g_group.n = 0;
+        zk::Enter back(0);
+        return back.rc;
+    }
+    ZK_ENTER;
+    dist_destroy(C);
+    return 0;
+}
+
 int zkgpu_dist_rows(uint64_t **rows, uint64_t *nrows, uint64_t *ncols, uint64_t **subtree)
 {
     ZK_ENTER;

@@ -183,8 +183,12 @@ __device__ __forceinline__ LaneInfo decode_lane(const PassParams &P, u64 Q)
     return L;
 }
 
+// resident threads per SM the kernel is compiled for: 512 keeps 128 registers per thread (no spills); 768 spills 4-76 bytes
+#ifndef ZK_TILE_OCC
+#define ZK_TILE_OCC 512
+#endif
 template <int LR1, int LR2, bool INV>
-__global__ void __launch_bounds__(TileCfg<LR1, LR2>::THREADS, 512 / TileCfg<LR1, LR2>::THREADS) ntt_tile_kernel(const PassParams P, const u32 ntiles)
+__global__ void __launch_bounds__(TileCfg<LR1, LR2>::THREADS, ZK_TILE_OCC / TileCfg<LR1, LR2>::THREADS) ntt_tile_kernel(const PassParams P, const u32 ntiles)
 {
     using Cfg = TileCfg<LR1, LR2>;
     constexpr int R1 = Cfg::R1, R2 = Cfg::R2, R = Cfg::R, TG = Cfg::TG, THREADS = Cfg::THREADS;

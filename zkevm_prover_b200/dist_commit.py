@@ -362,6 +362,10 @@ class CDist:
         self.zk._check(self.zk.lib().zkgpu_dist_rows(ct.byref(p), ct.byref(r), ct.byref(c), ct.byref(sub)))
         return p.value, r.value, c.value, sub.value
 
+    def close(self):
+        """Leave the job (zkgpu_dist_finalize); call it before torch.distributed is torn down."""
+        self.zk._check(self.zk.lib().zkgpu_dist_finalize())
+
     def exchange(self):
         """'stores' (peer stores fused into the LDE's last pass), 'dma' (copy engines) or 'nccl' (ncclSend/ncclRecv)."""
         ct = self.ct
