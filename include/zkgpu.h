@@ -102,6 +102,11 @@ int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t num_c
  * writes).  proof has width + 4*log2(height) words.  source / nodes / proof may each be host or device pointers. */
 int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *nodes, uint64_t width, uint64_t height, uint64_t idx);
 
+/* the same for nqueries rows at once (FRIProve::prove asks every tree for nQueries proofs, friProve.cpp:144-160, 219-235): one launch
+ * and one copy instead of one of each per query.  idx is a host array; proofs receives nqueries * (width + 4*log2(height)) words. */
+int zkgpu_group_proofs(uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width, uint64_t height, const uint64_t *idx,
+                       uint64_t nqueries);
+
 /* ---- the commit stage as one call: Starks::genProof steps 1-3 (src/starkpil/starks.cpp:51-58, 133-139, 214-220):
  * ntt.extendPol(out_ext, in, NExt, N, ncols) followed by MerkleTreeGL(NExt, ncols, out_ext).merkelize().
  * out_ext: n_extended x ncols, tree: (2*n_extended - 1)*4 words.  Here each of the three pointers may independently

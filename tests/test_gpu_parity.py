@@ -385,6 +385,14 @@ def test_group_proof_from_device_resident_tree():
         assert_eq(want[:c], ext[idx], "row")
         assert_eq(dev.getGroupProof(idx), want, "device proof %d" % idx)
         assert_eq(mixed.getGroupProof(idx), want, "mixed proof %d" % idx)
+    # the batch form (FRIProve::prove asks every tree for nQueries proofs, friProve.cpp:144-160): one launch, one copy
+    idxs = [0, 1, 1000, n * b - 1, 77, 77, 513]
+    want = np.stack([host.getGroupProof(i) for i in idxs])
+    assert_eq(zk.group_proofs(dev, idxs), want, "batch, device buffers")
+    assert_eq(zk.group_proofs(host, idxs), want, "batch, host buffers")
+    assert_eq(zk.group_proofs(mixed, idxs), want, "batch, mixed buffers")
+    with pytest.raises(zk.ZkGpuError):
+        zk.group_proofs(dev, [0, n * b])
 
 
 # ------------------------------------------------------------------------------------------------ large shapes, host pipelines

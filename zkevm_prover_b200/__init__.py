@@ -18,7 +18,7 @@ import pathlib
 import numpy as np
 
 __all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL", "FRIProve",
-           "extend_and_merkelize", "stage4_commit", "invalidate", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
+           "extend_and_merkelize", "stage4_commit", "invalidate", "group_proofs", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
 
 GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
 import os
@@ -55,6 +55,7 @@ ABI_SYMBOLS = {
     "zkgpu_extend_pol": (_int, [_vp, _vp, _vp, _u64, _u64, _u64, _vp]),
     "zkgpu_reverse_permutation": (_int, [_vp, _vp, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_group_proof": (_int, [_vp, _vp, _vp, _u64, _u64, _u64]),
+    "zkgpu_group_proofs": (_int, [_vp, _vp, _vp, _u64, _u64, _vp, _u64]),
     "zkgpu_hash_full_result": (_int, [_vp, _vp, _u64]),
     "zkgpu_linear_hash": (_int, [_vp, _vp, _u64]),
     "zkgpu_merkletree": (_int, [_vp, _vp, _u64, _u64, _u64]),
@@ -259,6 +260,14 @@ class MerkleTreeGL:
         proof = np.zeros(self.width + 4 * self.MerkleProofSize(), dtype=np.uint64)
         _check(lib().zkgpu_group_proof(_ptr(proof), _ptr(self.source), _ptr(self.nodes), self.width, self.height, idx))
         return proof
+
+
+def group_proofs(tree, idxs):
+    """MerkleTreeGL::getGroupProof for a batch of row indices (one launch, one copy): array of len(idxs) proofs."""
+    idx = np.ascontiguousarray(idxs, dtype=np.uint64)
+    out = np.zeros((idx.size, tree.width + 4 * tree.MerkleProofSize()), dtype=np.uint64)
+    _check(lib().zkgpu_group_proofs(_ptr(out), _ptr(tree.source), _ptr(tree.nodes), tree.width, tree.height, _ptr(idx), idx.size))
+    return out
 
 
 def build_const_tree(image, const_pols, nBits, nBitsExt, nPols):

@@ -105,6 +105,27 @@ __global__ void group_proof_kernel(u64 *proof, const u64 *row, const u64 *nodes,
     }
 }
 
+// the same for a batch of queries: block q serves idx[q] (FRIProve::prove asks for nQueries proofs per tree, friProve.cpp:144-160)
+__global__ void group_proofs_kernel(u64 *proofs, const u64 *source, const u64 *nodes, u64 width, u64 height, const u64 *idx, u64 proof_words)
+{
+    const u64 i0 = idx[blockIdx.x];
+    u64 *proof = proofs + (u64)blockIdx.x * proof_words;
+    const u64 *row = source + i0 * width;
+    for (u64 c = threadIdx.x; c < width; c += blockDim.x) proof[c] = row[c];
+    if (threadIdx.x < 4)
+    {
+        u64 off = 0, n = height, i = i0, lvl = 0;
+        while (n > 1)
+        {
+            proof[width + 4 * lvl + threadIdx.x] = nodes[off + (i ^ 1) * 4 + threadIdx.x];
+            off += n * 4;
+            n >>= 1;
+            i >>= 1;
+            lvl++;
+        }
+    }
+}
+
 __global__ void field_op_kernel(int op, u64 *out, const u64 *a, const u64 *b, u64 n)
 {
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
@@ -1212,6 +1233,45 @@ int zkgpu_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *n
         ZK_CUDA(cudaMemcpyAsync(proof, d_proof, proof_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
         ZK_CUDA(cudaStreamSynchronize(st));
     }
+    return 0;
+}
+
+int zkgpu_group_proofs(uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width, uint64_t height, const uint64_t *idx,
+                       uint64_t nqueries)
+{
+    if (nqueries == 0) return 0;
+    if (height == 0 || !idx || !proofs)
+    {
+        set_error("getGroupProof (batch): NULL argument or empty tree");
+        return -1;
+    }
+    for (u64 q = 0; q < nqueries; q++)
+        if (idx[q] >= height)
+        {
+            set_error("getGroupProof (batch): idx[%llu] = %llu out of range (height %llu)", (unsigned long long)q, (unsigned long long)idx[q],
+                      (unsigned long long)height);
+            return -1;
+        }
+    const unsigned levels = ilog2(height);
+    const u64 proof_words = width + 4 * (u64)levels;
+    const bool src_dev = width == 0 || is_device_ptr(source), nodes_dev = levels == 0 || is_device_ptr(nodes);
+    if (!src_dev || !nodes_dev)
+    {
+        // buffers on the host (or mixed): the single-proof entry handles every combination
+        for (u64 q = 0; q < nqueries; q++) ZK_TRY(zkgpu_group_proof(proofs + q * proof_words, source, nodes, width, height, idx[q]));
+        return 0;
+    }
+    ZK_ENTER;
+    cudaStream_t st = C.cur;
+    const bool proof_dev = is_device_ptr(proofs);
+    ZK_TRY(ctx_ensure_scratch(C, nqueries * (proof_words + 1)));
+    u64 *d_idx = C.scratch, *d_proofs = proof_dev ? proofs : C.scratch + nqueries;
+    ZK_CUDA(cudaMemcpyAsync(d_idx, idx, nqueries * sizeof(u64), cudaMemcpyHostToDevice, st));
+    group_proofs_kernel<<<(unsigned)nqueries, 256, 0, st>>>(d_proofs, source, nodes, width, height, d_idx, proof_words);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    if (!proof_dev) ZK_CUDA(cudaMemcpyAsync(proofs, d_proofs, nqueries * proof_words * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    ZK_CUDA(cudaStreamSynchronize(st)); // idx is the caller's host buffer
     return 0;
 }
 
