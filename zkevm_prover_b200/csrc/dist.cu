@@ -240,9 +240,7 @@ static int dist_barrier(Dist &D, cudaStream_t after, cudaStream_t then, cudaEven
 // column ownership: the row is cut into rounds x world consecutive pieces, piece (k, g) belonging to rank g in round k.
 // Every round but the last covers a whole number of 8-column sponge blocks (so absorbing round by round chunks the row
 // exactly as linear_hash does, poseidon_goldilocks.cpp:240-256); inside a round the columns are dealt out evenly.
-// Device-resident input: one round (stores) or two (staged exchange).  Host input: the rounds ramp up (2 blocks per rank,
-// 4, then rounds of at most 8) so that only the copy of the first small piece is exposed, and down again (3, 2) so that
-// little is left to compute after the last copy.
+// Device-resident input: one round (stores) or two (staged exchange).  Host input: uniform small rounds (below).
 // ---------------------------------------------------------------------------------------------------
 struct Plan
 {
@@ -269,31 +267,16 @@ static int make_plan(Plan &pl, u64 ncols, int world, bool host_input)
     }
     else
     {
-        u64 left = blocks;
-        const u64 wants[2] = {2 * (u64)world, 4 * (u64)world};
-        for (u64 want : wants)
-            if (left >= want + 4 * (u64)world)
-            {
-                per_round[nr++] = want;
-                left -= want;
-            }
-        // ... and ramp down again: when the host link is the bottleneck (8 GPUs share it: 20-24 GB/s each) everything that
-        // is still to be computed after the LAST copy lands is exposed, so the last rounds are small (3 and 2 blocks per rank)
-        u64 tail[2];
-        int nt = 0;
-        if (left >= 9 * (u64)world)
-        {
-            tail[nt++] = 3 * (u64)world;
-            tail[nt++] = 2 * (u64)world;
-        }
-        else if (left >= 4 * (u64)world)
-            tail[nt++] = 2 * (u64)world;
-        for (int i = 0; i < nt; i++) left -= tail[i];
-        u64 k = (left + 8 * (u64)world - 1) / (8 * (u64)world);
+        // Host input: uniform small rounds, two sponge blocks (16 columns) per rank and round, more when that would need more
+        // than 14 rounds.  With 8 GPUs the host link is the bottleneck (20-24 GB/s per GPU): everything still to be computed
+        // after the LAST copy lands is exposed, and a round's transform + sponge (32 ms) hides under the next round's copy
+        // (49 ms).  Measured at 8 GPUs, H: ramp 16/32/35 columns per rank 390 ms, ramp up + down 372 ms
+        // (profiles/r2_dist_timeline_n8_e2e_rampdown.txt: 100 ms of sponge left after the last copy), uniform rounds: see DESIGN.md.
+        u64 per = 2 * (u64)world;
+        if ((blocks + per - 1) / per > 14) per = (blocks + 13) / 14;
+        u64 k = blocks / per; // floor: no round narrower than `per` blocks (pieces under 16 columns take the slow narrow kernel)
         if (k < 1) k = 1;
-        if (k > (u64)(MAX_ROUNDS - nr - nt)) k = MAX_ROUNDS - nr - nt;
-        for (u64 i = 0; i < k; i++) per_round[nr++] = left / k + (i < left % k ? 1 : 0);
-        for (int i = 0; i < nt; i++) per_round[nr++] = tail[i];
+        for (u64 i = 0; i < k; i++) per_round[nr++] = blocks / k + (i < blocks % k ? 1 : 0);
     }
     pl.rounds = nr;
     u64 c = 0;
