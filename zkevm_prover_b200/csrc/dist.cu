@@ -127,7 +127,9 @@ struct Dist
     ncclComm_t comm = nullptr;
     cudaStream_t cs = nullptr; // every NCCL operation of this rank is issued here
     cudaStream_t xs = nullptr; // EX_DMA: the peer copies
-    cudaEvent_t ev_cp = nullptr;
+    cudaStream_t sa = nullptr; // the sponge: its own stream, so that the absorption of round k and the transform of round k+1
+                               // start in whichever order their inputs arrive (exchange of k / host copy of k+1)
+    cudaEvent_t ev_cp = nullptr, ev_sa = nullptr;
     cudaEvent_t ev_lde[MAX_ROUNDS] = {}, ev_bar[MAX_ROUNDS] = {}, ev_unp[MAX_ROUNDS] = {}, ev_a = nullptr, ev_b = nullptr;
     u64 *flag = nullptr;                                   // barrier word
     u64 *rows = nullptr;                                   // this rank's row shard of the extended trace, R x ncols
@@ -208,6 +210,8 @@ static int dist_create(Ctx &C, int rank, int world, ncclComm_t comm, bool single
     ZK_CUDA(cudaStreamCreateWithPriority(&D->cs, cudaStreamNonBlocking, prio_hi));
     ZK_CUDA(cudaStreamCreateWithPriority(&D->xs, cudaStreamNonBlocking, prio_hi));
     ZK_CUDA(cudaEventCreateWithFlags(&D->ev_cp, cudaEventDisableTiming));
+    ZK_CUDA(cudaEventCreateWithFlags(&D->ev_sa, cudaEventDisableTiming));
+    ZK_CUDA(cudaStreamCreateWithFlags(&D->sa, cudaStreamNonBlocking));
     for (int i = 0; i < MAX_ROUNDS; i++)
     {
         ZK_CUDA(cudaEventCreateWithFlags(&D->ev_lde[i], cudaEventDisableTiming));
@@ -485,6 +489,12 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
     mark("call", 0, st);
     // nobody may still be reading its rows (previous commit) when a peer starts storing into them
     ZK_TRY(dist_barrier(D, st, st, D.ev_a, D.ev_b));
+    // Host input: the sponge runs on its own stream, so that the absorption of round k and the transform of round k+1 start in
+    // whichever order their inputs arrive (the exchange of k / the host copy of k+1): with the host link as the bottleneck the
+    // sponge no longer queues behind a transform that is itself waiting for its copy (2 GPUs e2e 801 -> 759 ms).  Device input:
+    // one stream — run side by side the two kernels only slow each other down (2 GPUs 691.8 -> 707.8 ms).
+    cudaStream_t sa = host_input ? D.sa : st;
+    ZK_CUDA(cudaStreamWaitEvent(sa, D.ev_b, 0)); // the sponge stream starts after everything the caller queued before this call
 
     auto issue_h2d = [&](int k) -> int {
         const int b = k & 1;
@@ -501,7 +511,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         return 0;
     };
     auto absorb_round = [&](int k) -> int {
-        ZK_CUDA(cudaStreamWaitEvent(st, D.ev_bar[k], 0));
+        ZK_CUDA(cudaStreamWaitEvent(sa, D.ev_bar[k], 0));
         if (ex == EX_NCCL)
         {
             const u64 *rb = D.recv_buf + (size_t)(k & 1) * R * rwmax;
@@ -512,18 +522,18 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
                 {
                     u64 blocks = (R * w + 255) / 256;
                     if (blocks > (u64)C.num_sms * 32) blocks = (u64)C.num_sms * 32;
-                    dist_unpack_kernel<<<(unsigned)blocks, 256, 0, st>>>(D.rows + pl.c0[k][g], ncols, rb, R, w);
+                    dist_unpack_kernel<<<(unsigned)blocks, 256, 0, sa>>>(D.rows + pl.c0[k][g], ncols, rb, R, w);
                     ZK_LAUNCHED();
                     ZK_CUDA(cudaGetLastError());
                 }
                 rb += R * w;
             }
-            ZK_CUDA(cudaEventRecord(D.ev_unp[k], st));
+            ZK_CUDA(cudaEventRecord(D.ev_unp[k], sa));
         }
         if (ext_host && pl.round_w[k])
         {
             // this round's columns of my rows are complete: send them home while the sponge runs
-            ZK_CUDA(cudaEventRecord(C.out_ready[0], st));
+            ZK_CUDA(cudaEventRecord(C.out_ready[0], sa));
             ZK_CUDA(cudaStreamWaitEvent(C.d2h, C.out_ready[0], 0));
             ZK_CUDA(cudaMemcpy2DAsync(ext_host + (size_t)me * R * ncols + pl.round_c0[k], ncols * sizeof(u64), D.rows + pl.round_c0[k],
                                       ncols * sizeof(u64), pl.round_w[k] * sizeof(u64), R, cudaMemcpyDeviceToHost, C.d2h));
@@ -531,11 +541,11 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         if (ncols > 4 && pl.round_w[k])
         {
             int e0, e1;
-            ZK_TRY(ctx_pipe_event(C, &e0, st));
-            ZK_TRY(merkle_absorb(D.sub, D.rows + pl.round_c0[k], pl.round_w[k], ncols, R, k == 0, st));
-            ZK_TRY(ctx_pipe_event(C, &e1, st));
+            ZK_TRY(ctx_pipe_event(C, &e0, sa));
+            ZK_TRY(merkle_absorb(D.sub, D.rows + pl.round_c0[k], pl.round_w[k], ncols, R, k == 0, sa));
+            ZK_TRY(ctx_pipe_event(C, &e1, sa));
             C.segs.push_back({1, e0, e1});
-            mark("abs-", k, st);
+            mark("abs-", k, sa);
         }
         return 0;
     };
@@ -559,6 +569,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
             src = D.in_buf + (size_t)b * n * wmax;
             src_ld = w;
         }
+        if (k >= 2 && ex != EX_STORES) ZK_CUDA(cudaStreamWaitEvent(st, D.ev_bar[k - 2], 0)); // staging slot b has been shipped
         int e0, e1;
         mark("lde+", k, st);
         ZK_TRY(ctx_pipe_event(C, &e0, st));
@@ -624,12 +635,12 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
     {
         // rows of <= 4 words are copied, not hashed (poseidon_goldilocks.cpp:234-239)
         int e0, e1;
-        ZK_TRY(ctx_pipe_event(C, &e0, st));
-        ZK_TRY(merkle_leaves(D.sub, D.rows, ncols, ncols, R, st));
-        ZK_TRY(ctx_pipe_event(C, &e1, st));
+        ZK_TRY(ctx_pipe_event(C, &e0, sa));
+        ZK_TRY(merkle_leaves(D.sub, D.rows, ncols, ncols, R, sa));
+        ZK_TRY(ctx_pipe_event(C, &e1, sa));
         C.segs.push_back({1, e0, e1});
     }
-    ZK_CUDA(cudaEventRecord(C.ev[2], st));
+    ZK_CUDA(cudaEventRecord(C.ev[2], sa));
     // ---- stitch: level l of the global tree = the ranks' slices side by side (l <= log2 R), then the top over the sub-roots.
     // The leaf level is half of all the bytes: it travels to rank 0 while the node levels are being hashed.
     u64 soff[40], scnt[40], goff[40], gcnt[40];
@@ -654,20 +665,18 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         ZK_CUDA(cudaStreamWaitEvent(D.cs, C.ev[2], 0));
         ZK_TRY(ship_levels(0, 1));
     }
-    ZK_TRY(merkle_levels(D.sub, R, st));
-    ZK_CUDA(cudaEventRecord(D.ev_a, st));
+    ZK_TRY(merkle_levels(D.sub, R, sa));
+    ZK_CUDA(cudaEventRecord(D.ev_a, sa));
     ZK_CUDA(cudaStreamWaitEvent(D.cs, D.ev_a, 0));
     u64 *top_dst = (me == 0 && tree_d) ? tree_d + goff[LR] : D.top;
     ZK_NCCL(g_nccl.AllGather(D.sub + soff[LR], top_dst, 4, ncclUint64, D.comm, D.cs));
-    if (gather)
-    {
-        if (LR > 1) ZK_TRY(ship_levels(1, LR));
-        if (me == 0)
-            for (int l = 0; l < LR; l++)
-                ZK_CUDA(cudaMemcpyAsync(tree_d + goff[l], D.sub + soff[l], scnt[l] * 32, cudaMemcpyDeviceToDevice, st));
-    }
+    if (gather && LR > 1) ZK_TRY(ship_levels(1, LR));
     ZK_CUDA(cudaEventRecord(D.ev_b, D.cs));
-    ZK_CUDA(cudaStreamWaitEvent(st, D.ev_b, 0));
+    ZK_CUDA(cudaStreamWaitEvent(st, D.ev_b, 0)); // cs waited for the sponge stream (ev_a): st is now behind both
+    ZK_CUDA(cudaStreamWaitEvent(st, D.ev_a, 0));
+    if (gather && me == 0)
+        for (int l = 0; l < LR; l++)
+            ZK_CUDA(cudaMemcpyAsync(tree_d + goff[l], D.sub + soff[l], scnt[l] * 32, cudaMemcpyDeviceToDevice, st));
     if (me == 0) ZK_TRY(merkle_levels(top_dst, (u64)G, st));
     ZK_CUDA(cudaEventRecord(C.ev[3], st));
     C.timed = true;
@@ -912,6 +921,7 @@ static void dist_destroy(Ctx &C)
     cudaStreamSynchronize(C.cur);
     cudaStreamSynchronize(D->cs);
     cudaStreamSynchronize(D->xs);
+    cudaStreamSynchronize(D->sa);
     if (!D->single_process)
         for (int g = 0; g < D->world; g++)
             if (D->ipc_open[g]) cudaIpcCloseMemHandle(D->ipc_open[g]);
@@ -921,6 +931,7 @@ static void dist_destroy(Ctx &C)
     if (D->comm) g_nccl.CommDestroy(D->comm);
     cudaStreamDestroy(D->cs);
     cudaStreamDestroy(D->xs);
+    cudaStreamDestroy(D->sa);
     delete D;
     C.dist = nullptr;
 }
