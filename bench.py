@@ -446,7 +446,9 @@ def run_ours(args):
     if tp.exists():
         tj = json.loads(tp.read_text())
         traffic = tj.get("absorb_kernel@%dx%d/%d" % (args.log_rows, c, world))
-        traffic_note = "ncu --set full capture (profiles/), dram__bytes_read.sum + dram__bytes_write.sum summed over the step's launches"
+        traffic_note = "ncu capture (profiles/), dram__bytes_read.sum + dram__bytes_write.sum summed over the step's launches"
+        if world > 1 and traffic is not None:
+            traffic_note = tj.get("_note_multi", traffic_note)
         if traffic is None and tj.get("absorb_kernel@%dx%d/1" % (args.log_rows, c)) is not None:
             # the same kernel over 1/world of the rows per rank: the 1-GPU capture scaled, not a capture of this run
             traffic = tj["absorb_kernel@%dx%d/1" % (args.log_rows, c)] / world

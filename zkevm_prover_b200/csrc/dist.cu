@@ -117,7 +117,8 @@ static int exchange_wanted()
     }();
     return w;
 }
-static int g_exchange = EX_STORES; // what the job actually uses (set when peer access is known); read by zkgpu_dist_plan
+static int g_exchange = -1; // what the job actually uses (set when peer access is known); before that: what is wanted
+static int exchange_now() { return g_exchange >= 0 ? g_exchange : exchange_wanted(); }
 
 struct Dist
 {
@@ -259,7 +260,7 @@ static int make_plan(Plan &pl, u64 ncols, int world, bool host_input)
     const u64 blocks = (ncols + 7) / 8;
     u64 per_round[MAX_ROUNDS];
     int nr = 0;
-    if (blocks == 0 || (!host_input && g_exchange == EX_STORES))
+    if (blocks == 0 || (!host_input && exchange_now() == EX_STORES))
         per_round[nr++] = blocks;
     else if (!host_input)
     {
@@ -463,7 +464,7 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
     }
     ZK_TRY(ctx_ensure_scratch(C, 2 * n * (wmax ? wmax : 1)));
     if (host_input) ZK_TRY(dev_realloc(&D.in_buf, &D.in_cap, 2 * n * wmax));
-    const int ex = g_exchange;
+    const int ex = exchange_now();
     if (ex != EX_STORES) ZK_TRY(dev_realloc(&D.ext_buf, &D.ext_cap, 2 * n_ext * wmax));
     if (ex == EX_NCCL) ZK_TRY(dev_realloc(&D.recv_buf, &D.recv_cap, 2 * R * rwmax));
     const bool tree_is_dev = tree != nullptr && is_device_ptr(tree);
@@ -861,7 +862,7 @@ int zkgpu_dist_info(int *rank, int *world, int *peer_stores)
     ZK_ENTER;
     if (rank) *rank = C.dist ? C.dist->rank : 0;
     if (world) *world = g_group.n ? g_group.n : (C.dist ? C.dist->world : 1);
-    if (peer_stores) *peer_stores = C.dist ? (g_exchange == EX_STORES ? 1 : g_exchange == EX_DMA ? 2 : 0) : 0;
+    if (peer_stores) *peer_stores = C.dist ? (exchange_now() == EX_STORES ? 1 : exchange_now() == EX_DMA ? 2 : 0) : 0;
     return 0;
 }
 
