@@ -96,6 +96,28 @@ int zkgpu_merkletree(uint64_t *tree, const uint64_t *input, uint64_t num_cols, u
 /* merkletree_batch (poseidon_goldilocks.cpp:302-352) */
 int zkgpu_merkletree_batch(uint64_t *tree, const uint64_t *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size,
                            uint64_t dim);
+/* The same tree as zkgpu_merkletree_batch, for callers that cannot allocate device memory.  (This entry point has no
+ * counterpart in the reference: its CPU code simply mallocs the per-batch digests, poseidon_goldilocks.cpp:302-352.)
+ * Who needs it: a prover that reserves the whole GPU for its own arena when it starts (cudaMalloc then has nothing
+ * left to give, and the stream-ordered pool behind cudaMallocAsync cannot grow), a service whose device-memory budget is
+ * fixed by its operator so that no library may allocate behind its back, and a proving loop that must not stall on the
+ * driver's allocator (a pool that has to grow or trim takes a device-wide lock and may synchronise).
+ * zkgpu_merkletree_batch asks the stream-ordered allocator for num_rows * ceil(num_cols / batch_size) * 4 words of
+ * digest scratch on every call; this variant keeps that scratch in a fixed array inside the library image instead,
+ * 2^20 words = 8 MiB, which every GPU that loads libzkgpu.so holds until the process exits.  It calls no cudaMalloc / cudaFree / cudaMallocAsync and no routine that allocates.
+ *   - tree and input must be DEVICE pointers (host data would have to be staged, which needs memory); tree 16-byte aligned.
+ *   - Shapes whose scratch exceeds 2^20 words (e.g. more than 2^14 rows at 16 batches) are refused with an error (-1);
+ *     nothing is launched.  Use zkgpu_merkletree_batch for those.
+ *   - The first call on each device looks up the array's device address (and, if no other entry point ran there yet,
+ *     creates the library's context and uploads the Poseidon constants).  Make that first call before any stream
+ *     capture begins.
+ *   - All calls on one device share the one array.  It still holds the previous call's digests when the next one starts;
+ *     that is harmless (every row writes its digests before reading them), but two calls whose kernels overlap on the
+ *     GPU (the library stream was switched with zkgpu_set_stream between them) would overwrite each other's digests:
+ *     keep calls to this entry point ordered on one stream per device.
+ * Work is enqueued on the library stream and the call returns without waiting, as for every device-pointer call. */
+int zkgpu_merkletree_batch_noalloc(uint64_t *tree, const uint64_t *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size,
+                                   uint64_t dim);
 
 /* MerkleTreeGL::getGroupProof (src/starkpil/merkleTree/merkleTreeGL.cpp:12-35): proof[0 .. width) = row idx of source,
  * then for every level below the root the 4-word sibling digest (nodes is the level-major array zkgpu_merkletree

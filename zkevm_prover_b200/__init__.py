@@ -60,6 +60,7 @@ ABI_SYMBOLS = {
     "zkgpu_linear_hash": (_int, [_vp, _vp, _u64]),
     "zkgpu_merkletree": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_merkletree_batch": (_int, [_vp, _vp, _u64, _u64, _u64, _u64]),
+    "zkgpu_merkletree_batch_noalloc": (_int, [_vp, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_extend_and_merkelize": (_int, [_vp, _vp, _vp, _vp, _u64, _u64, _u64]),
     "zkgpu_build_const_tree": (_int, [_vp, _vp, _u64, _u64, _u64]),
     "zkgpu_lde_columns": (_int, [_vp, _u64, _vp, _u64, _u64, _u64, _u64]),

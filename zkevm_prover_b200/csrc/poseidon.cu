@@ -18,6 +18,7 @@
 #include "gl64.cuh"
 #include "zk_internal.h"
 #include "poseidon_constants.inc"
+#include "../../include/zkgpu.h"
 
 namespace zk {
 
@@ -836,4 +837,88 @@ int merkle_levels(u64 *tree, u64 nrows, cudaStream_t st)
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// zkgpu_merkletree_batch_noalloc: the batched Merkle tree for callers that must not allocate device memory.
+//
+// leaves_batch_kernel needs nrows * nbatches * 4 words of global memory for the per-batch digests of every row, beyond its
+// input and its output.  merkle_leaves_batch takes them from the stream-ordered allocator on every call.  This variant
+// keeps them in the module instead: a fixed array that the CUDA loader places in every device's memory when the library is
+// loaded there and that stays until the process exits (8 MiB per GPU, used or not).
+//
+// g_static_digests is a DEVICE symbol.  Host code must not hand its name to a kernel: on the host the name stands for a
+// shadow object of the runtime, not for device memory.  The device address comes from cudaGetSymbolAddress, asked once per
+// device while that device is current (the array exists once per device, at a different address on each).
+// ---------------------------------------------------------------------------------------------------
+#define ZK_STATIC_DIGEST_WORDS ((size_t)1 << 20)
+static __device__ __align__(256) u64 g_static_digests[ZK_STATIC_DIGEST_WORDS];
+static u64 *s_static_digests_addr[64] = {}; // per device ordinal; written under that device's context lock
+
+static int static_digests(Ctx &C, u64 **addr)
+{
+    if (C.device < 0 || C.device >= 64)
+    {
+        set_error("merkletree_batch_noalloc: device ordinal %d out of range", C.device);
+        return -1;
+    }
+    if (!s_static_digests_addr[C.device])
+    {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_digests); // the context's device is current (Enter)
+        if (e != cudaSuccess || !p)
+        {
+            set_error("merkletree_batch_noalloc: cudaGetSymbolAddress failed on device %d: %s", C.device, cudaGetErrorString(e));
+            cudaGetLastError();
+            return -2;
+        }
+        s_static_digests_addr[C.device] = (u64 *)p;
+    }
+    *addr = s_static_digests_addr[C.device];
+    return 0;
+}
+
 } // namespace zk
+
+extern "C" int zkgpu_merkletree_batch_noalloc(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t batch,
+                                              uint64_t dim)
+{
+    using namespace zk;
+    if (nrows == 0) return 0;
+    if (nrows & (nrows - 1))
+    {
+        set_error("merkletree_batch_noalloc: num_rows %llu is not a power of two", (unsigned long long)nrows);
+        return -1;
+    }
+    if (batch == 0)
+    {
+        set_error("merkletree_batch_noalloc: batch_size 0");
+        return -1;
+    }
+    const u64 nbatches = ncols ? (ncols + batch - 1) / batch : 1;
+    // nrows * nbatches * 4 without overflow: nrows <= 2^20 and nbatches <= 2^20 are both implied by the limit
+    if (nrows > ZK_STATIC_DIGEST_WORDS || nbatches > ZK_STATIC_DIGEST_WORDS || nrows * nbatches * 4 > ZK_STATIC_DIGEST_WORDS)
+    {
+        set_error("merkletree_batch_noalloc: num_rows * ceil(num_cols / batch_size) * 4 = %llu * %llu * 4 words of digest scratch exceed "
+                  "the built-in %llu words; use zkgpu_merkletree_batch (which allocates) for this shape",
+                  (unsigned long long)nrows, (unsigned long long)nbatches, (unsigned long long)ZK_STATIC_DIGEST_WORDS);
+        return -1;
+    }
+    ZK_ENTER;
+    if (!is_device_ptr(tree) || (ncols * dim != 0 && !is_device_ptr(input)))
+    {
+        set_error("merkletree_batch_noalloc: tree and input must be device pointers (staging host data would need an allocation)");
+        return -1;
+    }
+    if ((uintptr_t)tree & 15)
+    {
+        set_error("merkletree_batch_noalloc: the tree pointer must be 16-byte aligned");
+        return -1;
+    }
+    u64 *digests = nullptr;
+    ZK_TRY(static_digests(C, &digests));
+    cudaStream_t st = C.cur;
+    // every row writes its nbatches digests before it reads them back, so nothing in the array has to start at zero
+    leaves_batch_kernel<<<nblocks(nrows, 128), 128, 0, st>>>(tree, digests, input, ncols, dim, batch, nbatches, nrows);
+    ZK_LAUNCHED();
+    ZK_CUDA(cudaGetLastError());
+    return merkle_levels(tree, nrows, st);
+}
