@@ -3,7 +3,11 @@
   python gpu_dist_worker.py spawn WORLD LOG_N COLS LOG_B   process-per-GPU form (torch.distributed NCCL + zkgpu_dist_*)
   python gpu_dist_worker.py multi WORLD LOG_N COLS LOG_B   single-process form (zkgpu_init_multi + zkgpu_extend_and_merkelize)
 Each compares every word of the tree and of every row shard with the 1-GPU result of the same library (which the
-other GPU tests pin to the oracle / compiled reference), plus the oracle itself when the shape is small."""
+other GPU tests pin to the oracle / compiled reference), and for shapes up to 2^14 x 665 that 1-GPU result is first
+compared with the CPU oracle here, so that the multi-GPU words are checked against the oracle and not only against the
+library itself.  The single-process form also runs zkgpu_build_const_tree with host buffers after zkgpu_init_multi
+(it must hand the context over to the worker threads) and a commit in which one rank fails to allocate (every rank
+must come back with the error, and the next commit must work)."""
 import ctypes
 import os
 import pathlib
@@ -21,6 +25,13 @@ def single_gpu_result(zk, a, n, n_ext, c):
     ext = np.zeros((n_ext, c), dtype=np.uint64)
     tree = np.zeros((2 * n_ext - 1) * 4, dtype=np.uint64)
     zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n_ext, n, c)
+    if n * c <= (1 << 14) * 665:
+        from oracle_lib import Oracle
+        O = Oracle()
+        want_ext = O.extend_pol(a, n_ext)
+        assert np.array_equal(ext, want_ext), "1-GPU extended trace differs from the oracle"
+        assert np.array_equal(tree, O.merkletree(want_ext, c, n_ext)), "1-GPU tree differs from the oracle"
+        print("oracle checked", flush=True)
     return ext, tree
 
 
@@ -105,6 +116,27 @@ def main():
         zk.extend_and_merkelize(zk.NTT_Goldilocks(n), None, dtree, a, n_ext, n, c)
         zk.sync()
         assert np.array_equal(dtree.cpu().numpy().view(np.uint64), want_tree), "device-0 tree differs"
+        # buildConstTree with host buffers while the multi-GPU job exists: the commit inside it goes to the worker threads,
+        # which need the context the calling thread entered with
+        nb, nbe, npols = min(log_n, 10), min(log_n, 10) + 1, 5
+        cp = Oracle().fill((1 << nb) * npols, SEED, 7).reshape(1 << nb, npols)
+        img = np.zeros(2 + npols * (1 << nbe) + (2 * (1 << nbe) - 1) * 4, dtype=np.uint64)
+        zk.build_const_tree(img, cp, nb, nbe, npols)
+        cext = Oracle().extend_pol(cp, 1 << nbe)
+        assert img[0] == npols and img[1] == (1 << nbe)
+        assert np.array_equal(img[2:2 + npols * (1 << nbe)], cext.reshape(-1)), "const tree: extended polynomials differ"
+        assert np.array_equal(img[2 + npols * (1 << nbe):], Oracle().merkletree(cext, npols, 1 << nbe)), "const tree: nodes differ"
+        # one rank fails to allocate: all ranks return, the caller sees the error, the job stays usable
+        os.environ["ZKGPU_TEST_FAIL_RANK"] = str(world - 1)
+        try:
+            zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n_ext, n, c)
+            raise AssertionError("the failing rank was not reported")
+        except zk.ZkGpuError as e:
+            assert "ZKGPU_TEST_FAIL_RANK" in str(e) or "could not allocate" in str(e), str(e)
+        del os.environ["ZKGPU_TEST_FAIL_RANK"]
+        tree[:] = 0
+        zk.extend_and_merkelize(zk.NTT_Goldilocks(n), ext, tree, a, n_ext, n, c)
+        assert np.array_equal(tree, want_tree), "tree differs after a failed commit"
         r, w, ps = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
         zk._check(zk.lib().zkgpu_dist_info(ctypes.byref(r), ctypes.byref(w), ctypes.byref(ps)))
         zk._check(zk.lib().zkgpu_dist_finalize())

@@ -175,8 +175,26 @@ struct Group
         else
             cv.wait(lk, [&] { return phase != ph; });
     }
+    // every rank hands in its return code; all leave with the first failure (by rank) or 0.  Two barriers: the slots may be
+    // rewritten by the next agreement only after everyone has read them.
+    int agree(int rank, int rc, int *who = nullptr)
+    {
+        agree_rc[rank] = rc;
+        barrier();
+        int out = 0;
+        for (int g = 0; g < n && out == 0; g++)
+            if (agree_rc[g] < 0)
+            {
+                out = agree_rc[g];
+                if (who) *who = g;
+            }
+        barrier();
+        return out;
+    }
+    int agree_rc[MAX_WORLD] = {};
 };
 static Group g_group;
+static std::mutex g_multi_mu; // one single-process multi-GPU commit at a time (the ranks' barriers and NCCL calls must not interleave)
 
 static int dev_realloc(u64 **p, size_t *cap, size_t words)
 {
@@ -337,7 +355,21 @@ static int dist_setup_rows(Ctx &C, Dist &D, u64 need_words)
                 cudaIpcCloseMemHandle(D.ipc_open[g]);
                 D.ipc_open[g] = nullptr;
             }
-    ZK_TRY(dev_realloc(&D.rows, &D.rows_cap, need_words));
+    const int alloc_rc = dev_realloc(&D.rows, &D.rows_cap, need_words);
+    if (D.single_process)
+    {
+        // the other worker threads are on their way to the barriers below: a rank that ran out of memory must meet them there
+        // and everybody leaves with the error
+        int who = -1;
+        const int rc = g_group.agree(D.rank, alloc_rc, &who);
+        if (rc < 0)
+        {
+            if (who != D.rank) set_error("zkgpu dist: rank %d could not allocate its row shard", who);
+            return rc;
+        }
+    }
+    else
+        ZK_TRY(alloc_rc);
     for (int g = 0; g < D.world; g++) D.peer_rows[g] = nullptr;
     D.peer_rows[D.rank] = D.rows;
     bool ok = !force_nccl;
@@ -448,32 +480,69 @@ static int dist_commit_rank(Ctx &C, const PieceSrc *pieces, bool host_input, u64
         return -1;
     }
     cudaStream_t st = C.cur;
-    ZK_TRY(ctx_pipe_streams(C));
-    ZK_TRY(dist_setup_rows(C, D, R * ncols)); // also settles the exchange mode, which the plan depends on
+    // Everything that can fail for one rank alone (stream creation, allocations) comes first, and in the single-process form
+    // the worker threads then agree on the outcome: either all go on to the collectives below or all return the error.  A
+    // rank that left on its own would leave the others in an NCCL wait that never ends.
+    const int pipe_rc = ctx_pipe_streams(C);
+    if (D.single_process)
+    {
+        int who = -1;
+        const int rc = g_group.agree(me, pipe_rc, &who);
+        if (rc < 0)
+        {
+            if (who != me) set_error("zkgpu dist: rank %d could not create its copy streams", who);
+            return rc;
+        }
+    }
+    else
+        ZK_TRY(pipe_rc);
+    ZK_TRY(dist_setup_rows(C, D, R * ncols)); // also settles the exchange mode, which the plan depends on (agrees among the ranks itself)
     Plan pl;
-    ZK_TRY(make_plan(pl, ncols, G, host_input));
+    ZK_TRY(make_plan(pl, ncols, G, host_input)); // same arguments on every rank: fails for all or for none
     D.rows_n = R;
     D.rows_c = ncols;
     const u64 sub_words = (2 * R - 1) * 4;
-    ZK_TRY(dev_realloc(&D.sub, &D.sub_cap, sub_words));
     u64 wmax = 0, rwmax = 0;
     for (int k = 0; k < pl.rounds; k++)
     {
         if (pl.w[k][me] > wmax) wmax = pl.w[k][me];
         if (pl.round_w[k] > rwmax) rwmax = pl.round_w[k];
     }
-    ZK_TRY(ctx_ensure_scratch(C, 2 * n * (wmax ? wmax : 1)));
-    if (host_input) ZK_TRY(dev_realloc(&D.in_buf, &D.in_cap, 2 * n * wmax));
     const int ex = exchange_now();
-    if (ex != EX_STORES) ZK_TRY(dev_realloc(&D.ext_buf, &D.ext_cap, 2 * n_ext * wmax));
-    if (ex == EX_NCCL) ZK_TRY(dev_realloc(&D.recv_buf, &D.recv_cap, 2 * R * rwmax));
     const bool tree_is_dev = tree != nullptr && is_device_ptr(tree);
     u64 *tree_d = tree_is_dev ? tree : nullptr; // rank 0's device image of the whole tree, when there is one
-    if (me == 0 && gather && !tree_is_dev)
+    auto allocate = [&]() -> int {
+        ZK_TRY(dev_realloc(&D.sub, &D.sub_cap, sub_words));
+        ZK_TRY(ctx_ensure_scratch(C, 2 * n * (wmax ? wmax : 1)));
+        if (host_input) ZK_TRY(dev_realloc(&D.in_buf, &D.in_cap, 2 * n * wmax));
+        if (ex != EX_STORES) ZK_TRY(dev_realloc(&D.ext_buf, &D.ext_cap, 2 * n_ext * wmax));
+        if (ex == EX_NCCL) ZK_TRY(dev_realloc(&D.recv_buf, &D.recv_cap, 2 * R * rwmax));
+        if (me == 0 && gather && !tree_is_dev)
+        {
+            ZK_TRY(dev_realloc(&D.tree_dev, &D.tree_cap, (2 * n_ext - 1) * 4));
+            tree_d = D.tree_dev;
+        }
+        return 0;
+    };
+    int alloc_rc = allocate();
+    if (D.single_process && alloc_rc == 0 && getenv("ZKGPU_TEST_FAIL_RANK") && atoi(getenv("ZKGPU_TEST_FAIL_RANK")) == me)
     {
-        ZK_TRY(dev_realloc(&D.tree_dev, &D.tree_cap, (2 * n_ext - 1) * 4));
-        tree_d = D.tree_dev;
+        // test hook (tests/gpu_dist_worker.py): behave as if this rank had run out of device memory
+        set_error("zkgpu dist: cannot allocate (ZKGPU_TEST_FAIL_RANK=%d)", me);
+        alloc_rc = -4;
     }
+    if (D.single_process)
+    {
+        int who = -1;
+        const int rc = g_group.agree(me, alloc_rc, &who);
+        if (rc < 0)
+        {
+            if (who != me) set_error("zkgpu dist: rank %d could not allocate its buffers", who);
+            return rc;
+        }
+    }
+    else
+        ZK_TRY(alloc_rc);
 
     ctx_pipe_event(C, nullptr, st);
     C.segs.clear();
@@ -731,6 +800,15 @@ int dist_multi_commit(u64 *out_ext, u64 *tree, const u64 *input, u64 n_ext, u64 
         return -1;
     }
     const bool tree_dev = tree && is_device_ptr(tree);
+    if (tree_dev && ptr_device(tree) != g_group.ctx[0]->device)
+    {
+        set_error("zkgpu multi-GPU commit: a device tree must be memory of rank 0's device (%d), this one is on device %d",
+                  g_group.ctx[0]->device, ptr_device(tree));
+        return -1;
+    }
+    // Callers may be many host threads (the drop-in classes are used from OpenMP regions).  The worker threads of two commits
+    // would meet at the same barriers and enqueue on the same communicators in arbitrary order: one commit at a time.
+    std::lock_guard<std::mutex> one_at_a_time(g_multi_mu);
     Plan pl;
     ZK_TRY(make_plan(pl, ncols, G, true));
     int rcs[MAX_WORLD] = {};
@@ -739,12 +817,12 @@ int dist_multi_commit(u64 *out_ext, u64 *tree, const u64 *input, u64 n_ext, u64 
     for (int g = 0; g < G; g++)
         th.emplace_back([&, g]() {
             Enter en(g_group.ctx[g]->device);
-            if (en.rc < 0)
+            // the first agreement of the call: a rank that cannot take its context tells the others, and all of them return
+            const int all_in = g_group.agree(g, en.rc);
+            if (en.rc < 0 || all_in < 0)
             {
-                rcs[g] = en.rc;
-                snprintf(errs[g], sizeof(errs[g]), "%s", last_error());
-                // a rank that cannot even enter would leave the others waiting at the first barrier: nothing sane to do
-                // but report; contexts were created in zkgpu_init_multi, so this does not happen in practice
+                rcs[g] = en.rc < 0 ? en.rc : all_in;
+                snprintf(errs[g], sizeof(errs[g]), "%s", en.rc < 0 ? last_error() : "another rank could not enter its context");
                 return;
             }
             PieceSrc ps[MAX_ROUNDS];
