@@ -144,6 +144,19 @@ int zkgpu_extend_and_merkelize(void *ntt, uint64_t *out_ext, uint64_t *tree, con
  * guards against a buffer that was modified in between; zkgpu_invalidate(ptr) (NULL = everything) drops entries explicitly;
  * ZKGPU_FUSE_COMMIT=0 or zkgpu_tune(2, 0) turns the behaviour off. */
 int zkgpu_invalidate(const void *host_ptr);
+/* What the fingerprint covers, and the hazard that remains.  The first and the last row are compared word for word, and a
+ * keyed 64-bit checksum is taken over 2^20 words at positions drawn from a per-entry random seed: every word when the buffer
+ * has no more than that, and every word of any buffer with ZKGPU_CACHE_VERIFY=full in the environment (a threaded pass over
+ * the host buffer: about a second at 89 GB, still cheaper than uploading and hashing it again).  In the default mode a caller
+ * that rewrites a FEW words of a LARGE buffer between extendPol and merkelize() may go unnoticed and receive the tree of the
+ * old contents; such a caller must call zkgpu_invalidate, set ZKGPU_CACHE_VERIFY=full, or switch the cache off.  Another
+ * matrix at the same address (freed and re-allocated buffer) is caught in either mode.  The reference's genProof does not
+ * write between the two calls (starks.cpp:53-57).  Entries wait in pinned host memory (no device memory is held for a tree
+ * nobody has claimed), at most 4 of them and 5 GiB; an NTT_Goldilocks object two of whose trees went unclaimed stops hashing
+ * in extendPol (StarkRecursiveF builds BN128 trees on its extended traces, starkRecursiveF.cpp:198-200).
+ * zkgpu_cache_stats: out[0..3] = hits, misses, stale (fingerprint mismatch: tree recomputed), dropped unclaimed;
+ * out[4] = entries waiting now, out[5] = bytes of DEVICE memory they hold (0 unless pinned memory could not be had). */
+int zkgpu_cache_stats(uint64_t out[6]);
 
 /* ---- stage 4 of Starks::genProof on the device (src/starkpil/starks.cpp:261-293):
  *   nttExtended.INTT(qq1, q_2ns, NExt, qDim);  qq2[k*qDeg + p] = qq1[p*N + k] * shiftIn^p (shiftIn = (1/7)^N, :266-281);

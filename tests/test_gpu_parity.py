@@ -677,3 +677,71 @@ def test_commit_cache_serves_the_unchanged_call_pair():
     mt.merkelize()
     assert_eq(mt.nodes, O.merkletree(ext, c, n * b), "modified buffer")
 
+
+
+def test_commit_cache_notices_any_word_and_a_new_matrix_at_the_same_address():
+    """VERDICT r2 item 5 / ADVICE: a word changed anywhere in the buffer (not one of the two rows kept verbatim) between
+    extendPol and merkelize() must give the recomputed tree; so must another matrix of the same shape at the same address;
+    an entry nobody claims holds no device memory; the counters say what happened."""
+    n, c, b = 1 << 13, 45, 2
+    a = O.fill(n * c, SEED, 78).reshape(n, c)
+    ntt = zk.NTT_Goldilocks(n)
+    zk._check(zk.lib().zkgpu_tune(2, 1))
+    zk.invalidate()
+    s0 = zk.cache_stats()
+    ext = np.zeros((n * b, c), dtype=np.uint64)
+    ntt.extendPol(ext, a, n * b, n, c)
+    s1 = zk.cache_stats()
+    assert s1["entries"] == 1 and s1["device_bytes"] == 0, s1
+    ext[n * b // 5 + 3, 17] ^= np.uint64(1 << 40)  # an arbitrary interior word
+    mt = zk.MerkleTreeGL(n * b, c, ext)
+    mt.merkelize()
+    assert_eq(mt.nodes, O.merkletree(ext, c, n * b), "interior word changed")
+    s2 = zk.cache_stats()
+    assert s2["stale"] == s0["stale"] + 1 and s2["entries"] == 0, (s0, s2)
+    # same address, same shape, another matrix that agrees with the first on rows 0 and n-1
+    ntt.extendPol(ext, a, n * b, n, c)
+    other = O.fill(n * b * c, SEED, 79).reshape(n * b, c)
+    other[0, :] = ext[0, :]
+    other[-1, :] = ext[-1, :]
+    ext[:] = other
+    mt = zk.MerkleTreeGL(n * b, c, ext)
+    mt.merkelize()
+    assert_eq(mt.nodes, O.merkletree(other, c, n * b), "another matrix at the same address")
+    # an untouched buffer is still a hit
+    ntt.extendPol(ext, a, n * b, n, c)
+    launches = zk.lib().zkgpu_launch_count()
+    mt = zk.MerkleTreeGL(n * b, c, ext)
+    mt.merkelize()
+    assert zk.lib().zkgpu_launch_count() == launches
+    s3 = zk.cache_stats()
+    assert s3["hits"] == s0["hits"] + 1 and s3["stale"] == s0["stale"] + 2, (s0, s3)
+
+
+def test_commit_cache_gives_up_on_a_caller_that_never_merkelizes():
+    """StarkRecursiveF extends and then builds a BN128 tree (starkRecursiveF.cpp:198-200): after two trees of one
+    NTT_Goldilocks object went unclaimed, its extendPol stops hashing (no sponge launches, no entries)."""
+    n, c, b = 1 << 10, 24, 2
+    a = O.fill(n * c, SEED, 80).reshape(n, c)
+    zk._check(zk.lib().zkgpu_tune(2, 1))
+    zk.invalidate()
+    ntt = zk.NTT_Goldilocks(n)
+    bufs = [np.zeros((n * b, c), dtype=np.uint64) for _ in range(4)]
+    per_call = []
+    for ext in bufs:
+        l0 = zk.lib().zkgpu_launch_count()
+        ntt.extendPol(ext, a, n * b, n, c)
+        per_call.append(zk.lib().zkgpu_launch_count() - l0)
+    assert zk.cache_stats()["entries"] == 0, zk.cache_stats()
+    assert per_call[2] < per_call[0] and per_call[3] == per_call[2], per_call
+    want = O.extend_pol(a, n * b)
+    for ext in bufs:
+        assert_eq(ext, want, "extendPol")
+    # another object is unaffected, and merkelize() on its buffer is a hit
+    ntt2 = zk.NTT_Goldilocks(n)
+    ntt2.extendPol(bufs[0], a, n * b, n, c)
+    assert zk.cache_stats()["entries"] == 1
+    mt = zk.MerkleTreeGL(n * b, c, bufs[0])
+    mt.merkelize()
+    assert_eq(mt.nodes, O.merkletree(want, c, n * b), "tree")
+    zk.invalidate()

@@ -18,7 +18,7 @@ import pathlib
 import numpy as np
 
 __all__ = ["ZkGpuError", "lib", "lib_path", "ABI_SYMBOLS", "NTT_Goldilocks", "PoseidonGoldilocks", "MerkleTreeGL", "FRIProve",
-           "extend_and_merkelize", "stage4_commit", "invalidate", "group_proofs", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
+           "extend_and_merkelize", "stage4_commit", "invalidate", "cache_stats", "group_proofs", "build_const_tree", "fill", "stage_ms", "set_stream", "sync", "GOLDILOCKS_PRIME"]
 
 GOLDILOCKS_PRIME = 0xFFFFFFFF00000001
 import os
@@ -72,6 +72,7 @@ ABI_SYMBOLS = {
     "zkgpu_merkle_levels": (_int, [_vp, _u64]),
     "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
     "zkgpu_invalidate": (_int, [_vp]),
+    "zkgpu_cache_stats": (_int, [ctypes.POINTER(_u64)]),
     "zkgpu_stage4_commit": (_int, [_vp, _vp, _vp, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_init_multi": (_int, [_int]),
     "zkgpu_nccl_unique_id": (_int, [_vp]),
@@ -304,6 +305,13 @@ def stage4_commit(ntt_extended, cm4_2ns, tree, q_2ns, N_Extended, N, qDim, qDeg)
 def invalidate(host_buffer=None):
     """Drop commit-cache entries for this host buffer (None: all of them)."""
     _check(lib().zkgpu_invalidate(_ptr(host_buffer)))
+
+
+def cache_stats():
+    """Commit-cache counters: dict(hits, misses, stale, dropped, entries, device_bytes)."""
+    out = (_u64 * 6)()
+    _check(lib().zkgpu_cache_stats(out))
+    return dict(zip(("hits", "misses", "stale", "dropped", "entries", "device_bytes"), (int(x) for x in out)))
 
 
 def extend_and_merkelize(ntt, out_ext, tree, inp, N_Extended, N, ncols):

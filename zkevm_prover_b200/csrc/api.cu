@@ -7,6 +7,9 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <atomic>
+#include <chrono>
+#include <thread>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -492,12 +495,20 @@ struct Resident
 {
     const u64 *host = nullptr; // key: the caller's extended-trace buffer
     u64 nrows = 0, ncols = 0;
-    u64 *d_tree = nullptr;     // device copy of the finished tree (single-GPU path)
-    u64 *h_tree = nullptr;     // pinned host copy (multi-GPU path: every device wrote its slices)
+    u64 *d_tree = nullptr;     // device copy of the finished tree (only when no pinned slot could be had)
+    u64 *h_tree = nullptr;     // pinned host copy: an entry nobody claims must not hold device memory
+    const void *handle = nullptr; // the NTT_Goldilocks object whose extendPol made the entry
+    // fingerprint of the buffer as extendPol left it: the first and the last row word for word, and a keyed checksum of
+    // CACHE_SAMPLES words at positions drawn from a per-entry seed (every word when the buffer is smaller than that, or when
+    // ZKGPU_CACHE_VERIFY=full).  A caller cannot know which words are looked at.
+    u64 seed = 0, sum = 0;
+    bool full = false;
     std::vector<u64> rows_idx, rows_words;
 };
 static std::mutex g_cache_mu;
 static std::vector<Resident> g_cache; // process-wide: the key is a host pointer
+static u64 g_cache_stats[4] = {0, 0, 0, 0};               // hits, misses, stale, evicted (zkgpu_cache_stats)
+static std::map<const void *, int> g_unclaimed;           // per NTT handle: entries dropped without a merkelize() asking for them
 int g_fuse_commit = -1;               // -1: read ZKGPU_FUSE_COMMIT (default on)
 
 static bool fuse_enabled()
@@ -559,6 +570,11 @@ static void cache_invalidate(const void *p, size_t bytes)
         const bool hit = p == nullptr || (bytes == 0 ? p == (const void *)a : ((const char *)p < b && (const char *)p + bytes > a));
         if (hit)
         {
+            if (bytes != 0) // overwritten by a new extendPol before any merkelize() asked for it
+            {
+                g_unclaimed[r.handle]++;
+                g_cache_stats[3]++;
+            }
             cache_free(r);
             g_cache.erase(g_cache.begin() + i);
         }
@@ -566,43 +582,143 @@ static void cache_invalidate(const void *p, size_t bytes)
             i++;
     }
 }
+static const u64 CACHE_SAMPLES = (u64)1 << 20;
+static const size_t CACHE_MAX_ENTRIES = 4;                // a genProof has at most a handful of commit stages in flight
+static const size_t CACHE_MAX_BYTES = (size_t)5 << 30;    // of pinned host memory held for trees nobody has claimed yet
+static inline u64 mix64(u64 x)
+{
+    x ^= x >> 30;
+    x *= 0xBF58476D1CE4E5B9ull;
+    x ^= x >> 27;
+    x *= 0x94D049BB133111EBull;
+    x ^= x >> 31;
+    return x;
+}
+// order-independent keyed checksum of the host buffer: all words (full) or CACHE_SAMPLES pseudo-random positions
+static u64 cache_checksum(const u64 *host, u64 total, u64 seed, bool full)
+{
+    const u64 count = full ? total : CACHE_SAMPLES;
+    unsigned nt = std::thread::hardware_concurrency();
+    if (nt > (full ? 32u : 8u)) nt = full ? 32 : 8;
+    if (nt < 1 || count < ((u64)1 << 16)) nt = 1;
+    std::vector<u64> part(nt, 0);
+    auto work = [&](unsigned t) {
+        const u64 lo = count * t / nt, hi = count * (t + 1) / nt;
+        u64 acc = 0;
+        for (u64 k = lo; k < hi; k++)
+        {
+            const u64 pos = full ? k : mix64(seed + k) % total;
+            acc += mix64(host[pos] ^ (seed + pos * 0x9E3779B97F4A7C15ull));
+        }
+        part[t] = acc;
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto &t : th) t.join();
+    u64 acc = 0;
+    for (u64 v : part) acc += v;
+    return acc;
+}
 static void cache_fingerprint(Resident &r)
 {
-    const u64 picks[6] = {0, 1, r.nrows / 3, r.nrows / 2, r.nrows - 2, r.nrows - 1};
+    static std::atomic<u64> counter{0};
+    const char *e = getenv("ZKGPU_CACHE_VERIFY");
+    const u64 total = r.nrows * r.ncols;
+    r.full = (e && strcmp(e, "full") == 0) || total <= CACHE_SAMPLES;
+    r.seed = mix64((u64)std::chrono::steady_clock::now().time_since_epoch().count() ^ mix64((u64)(uintptr_t)r.host + counter.fetch_add(1)));
+    r.sum = cache_checksum(r.host, total, r.seed, r.full);
+    const u64 picks[2] = {0, r.nrows - 1};
     for (u64 i : picks)
-        if (i < r.nrows)
+        if (i < r.nrows && (r.rows_idx.empty() || r.rows_idx.back() != i))
         {
             r.rows_idx.push_back(i);
             r.rows_words.insert(r.rows_words.end(), r.host + i * r.ncols, r.host + (i + 1) * r.ncols);
         }
 }
+static size_t cache_bytes_locked()
+{
+    size_t b = 0;
+    for (auto &r : g_cache) b += (2 * r.nrows - 1) * 4 * sizeof(u64);
+    return b;
+}
 static void cache_put(Resident &&r)
 {
     std::lock_guard<std::mutex> lk(g_cache_mu);
-    while (g_cache.size() >= 4) // a genProof has at most a handful of commit stages in flight
+    const size_t mine = (2 * r.nrows - 1) * 4 * sizeof(u64);
+    while (!g_cache.empty() && (g_cache.size() >= CACHE_MAX_ENTRIES || cache_bytes_locked() + mine > CACHE_MAX_BYTES))
     {
+        g_unclaimed[g_cache.front().handle]++;
+        g_cache_stats[3]++;
         cache_free(g_cache.front());
         g_cache.erase(g_cache.begin());
     }
     g_cache.push_back(std::move(r));
 }
+// May extendPol of this NTT object hash on the way?  Not once two of its trees have gone unclaimed: the caller evidently does
+// not build Goldilocks trees on these buffers (StarkRecursiveF extends and then builds a BN128 tree,
+// starkRecursiveF.cpp:198-200), and the sponge would be wasted work.  In genProof every extendPol is followed by its
+// merkelize() before the next extendPol, so entries of this handle that are still waiting when a new one arrives count too.
+static bool cache_wanted(const void *handle)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    int waiting = 0;
+    for (auto &r : g_cache)
+        if (r.handle == handle) waiting++;
+    if (waiting >= 2 && g_unclaimed[handle] < 2)
+    {
+        g_unclaimed[handle] = 2;
+        for (size_t i = 0; i < g_cache.size();)
+            if (g_cache[i].handle == handle)
+            {
+                g_cache_stats[3]++;
+                cache_free(g_cache[i]);
+                g_cache.erase(g_cache.begin() + i);
+            }
+            else
+                i++;
+    }
+    return g_unclaimed[handle] < 2;
+}
+static void cache_forget_handle(const void *handle)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    g_unclaimed.erase(handle);
+}
 // the entry for this buffer if it is still what extendPol wrote; removed from the cache (the caller owns it now)
 static bool cache_take(const u64 *host, u64 nrows, u64 ncols, Resident *out)
 {
-    std::lock_guard<std::mutex> lk(g_cache_mu);
-    for (size_t i = 0; i < g_cache.size(); i++)
+    Resident r;
     {
-        Resident &r = g_cache[i];
-        if (r.host != host || r.nrows != nrows || r.ncols != ncols) continue;
-        bool same = true;
-        for (size_t k = 0; k < r.rows_idx.size() && same; k++)
-            same = memcmp(host + r.rows_idx[k] * ncols, r.rows_words.data() + k * ncols, ncols * sizeof(u64)) == 0;
-        if (same) *out = std::move(r);
-        else cache_free(r);
+        std::lock_guard<std::mutex> lk(g_cache_mu);
+        size_t i = 0;
+        for (; i < g_cache.size(); i++)
+            if (g_cache[i].host == host && g_cache[i].nrows == nrows && g_cache[i].ncols == ncols) break;
+        if (i == g_cache.size())
+        {
+            g_cache_stats[1]++;
+            return false;
+        }
+        r = std::move(g_cache[i]);
         g_cache.erase(g_cache.begin() + i);
-        return same;
     }
-    return false;
+    bool same = true;
+    for (size_t k = 0; k < r.rows_idx.size() && same; k++)
+        same = memcmp(host + r.rows_idx[k] * ncols, r.rows_words.data() + k * ncols, ncols * sizeof(u64)) == 0;
+    if (same) same = cache_checksum(host, nrows * ncols, r.seed, r.full) == r.sum; // outside the lock: may read the whole buffer
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    if (same)
+    {
+        g_cache_stats[0]++;
+        g_unclaimed[r.handle] = 0;
+        *out = std::move(r);
+    }
+    else
+    {
+        g_cache_stats[2]++;
+        cache_free(r);
+    }
+    return same;
 }
 
 // "device pointers only" entry points: reject host pointers and mis-aligned digest arrays (the kernels access leaves and
@@ -797,7 +913,11 @@ void *zkgpu_ntt_create(uint64_t max_domain_size, int extension)
     }
     return new NttHandle{max_domain_size, extension};
 }
-void zkgpu_ntt_destroy(void *h) { delete (NttHandle *)h; }
+void zkgpu_ntt_destroy(void *h)
+{
+    cache_forget_handle(h); // the address may come back for another object
+    delete (NttHandle *)h;
+}
 
 int zkgpu_ntt(void *, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, uint64_t *, int inverse, int extend)
 {
@@ -944,7 +1064,7 @@ int zkgpu_lde_columns(uint64_t *out, uint64_t out_ld, const uint64_t *in, uint64
     return lde_all(C, out, out_ld, in, in_ld, log_n, log_b, ncols, C.cur);
 }
 
-int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n_ext, uint64_t n, uint64_t ncols, uint64_t *)
+int zkgpu_extend_pol(void *ntt_handle, uint64_t *output, const uint64_t *input, uint64_t n_ext, uint64_t n, uint64_t ncols, uint64_t *)
 {
     if (n == 0 || ncols == 0 || n_ext == 0) return 0;
     unsigned log_n, log_b;
@@ -972,7 +1092,8 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
     // host pointers: column strips, host->device of strip s+1 and device->host of strip s-1 overlap the LDE of strip s.
     // With the commit cache on, the strips are hashed on the way (see Resident above) for the merkelize() that follows.
     cache_invalidate(output, n_ext * ncols * sizeof(u64));
-    if (dist_world_of_process() > 1 && fuse_enabled() && ncols > 4 && n_ext >= (u64)dist_world_of_process() && output != input)
+    const bool fuse = fuse_enabled() && ncols > 4 && cache_wanted(ntt_handle);
+    if (dist_world_of_process() > 1 && fuse && n_ext >= (u64)dist_world_of_process() && output != input)
     {
         // multi-GPU job (zkgpu_init_multi / ZKGPU_NGPU): all GPUs extend and hash; the tree waits in pinned host memory
         en__.lk.unlock(); // the worker threads lock their own contexts, device 0's included
@@ -980,6 +1101,7 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
         r.host = output;
         r.nrows = n_ext;
         r.ncols = ncols;
+        r.handle = ntt_handle;
         r.h_tree = pinned_take((2 * n_ext - 1) * 4);
         if (!r.h_tree)
         {
@@ -997,7 +1119,7 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
         return 0;
     }
     u64 *d_tree = nullptr;
-    if (fuse_enabled() && ncols > 4)
+    if (fuse)
     {
         if (cudaMalloc(&d_tree, (2 * n_ext - 1) * 4 * sizeof(u64)) != cudaSuccess)
         {
@@ -1026,7 +1148,19 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
         r.host = output;
         r.nrows = n_ext;
         r.ncols = ncols;
-        r.d_tree = d_tree;
+        r.handle = ntt_handle;
+        // the tree waits for its merkelize() in pinned host memory: an entry that is never claimed holds no device memory
+        const size_t tree_words = (2 * n_ext - 1) * 4;
+        r.h_tree = pinned_take(tree_words);
+        if (r.h_tree && cudaMemcpy(r.h_tree, d_tree, tree_words * sizeof(u64), cudaMemcpyDeviceToHost) == cudaSuccess)
+            cudaFree(d_tree);
+        else
+        {
+            cudaGetLastError();
+            if (r.h_tree) pinned_give(r.h_tree, tree_words);
+            r.h_tree = nullptr;
+            r.d_tree = d_tree;
+        }
         cache_fingerprint(r);
         cache_put(std::move(r));
     }
@@ -1036,6 +1170,17 @@ int zkgpu_extend_pol(void *, uint64_t *output, const uint64_t *input, uint64_t n
 int zkgpu_invalidate(const void *host_ptr)
 {
     cache_invalidate(host_ptr, 0);
+    return 0;
+}
+int zkgpu_cache_stats(uint64_t out[6])
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (int i = 0; i < 4; i++) out[i] = g_cache_stats[i];
+    out[4] = g_cache.size();
+    u64 dev = 0;
+    for (auto &r : g_cache)
+        if (r.d_tree) dev += (2 * r.nrows - 1) * 4 * sizeof(u64);
+    out[5] = dev;
     return 0;
 }
 
@@ -1514,7 +1659,14 @@ int zkgpu_tune(int key, int value)
     {
     case 0: g_absorb_threads = value == 512 ? 512 : 128; return 0;
     case 1: g_ntt_threads_per_sm_cap = value < 0 ? 0 : value; return 0;
-    case 2: g_fuse_commit = value ? 1 : 0; return 0; // commit cache: extendPol with host pointers also hashes (default on)
+    case 2:
+        g_fuse_commit = value ? 1 : 0;
+        if (value)
+        {
+            std::lock_guard<std::mutex> lk(g_cache_mu);
+            g_unclaimed.clear(); // switching the cache on again also forgives the handles it had given up on
+        }
+        return 0; // commit cache: extendPol with host pointers also hashes (default on)
     }
     set_error("zkgpu_tune: unknown key %d", key);
     return -1;
@@ -1527,11 +1679,16 @@ int zkgpu_build_const_tree(uint64_t *image, const uint64_t *const_pols, uint64_t
         set_error("buildConstTree: need nBits <= nBitsExt <= 32 and an image buffer");
         return -1;
     }
-    ZK_ENTER;
     const u64 n = (u64)1 << n_bits, n_ext = (u64)1 << n_bits_ext;
-    const u64 header[2] = {n_pols, n_ext}; // constTree[0] = nPols, constTree[1] = nExt (build_const_tree.cpp:576-577)
-    ZK_CUDA(cudaMemcpyAsync(image, header, sizeof(header), cudaMemcpyDefault, C.cur));
-    ZK_CUDA(cudaStreamSynchronize(C.cur)); // header[] is a stack buffer
+    {
+        // The context is held for the header only.  With a multi-GPU job (zkgpu_init_multi / ZKGPU_NGPU) and host buffers the
+        // commit below is done by one worker thread per device, and the worker of this thread's device must be able to
+        // take the same context: holding it across the call would block that worker while this thread waits for it.
+        ZK_ENTER;
+        const u64 header[2] = {n_pols, n_ext}; // constTree[0] = nPols, constTree[1] = nExt (build_const_tree.cpp:576-577)
+        ZK_CUDA(cudaMemcpyAsync(image, header, sizeof(header), cudaMemcpyDefault, C.cur));
+        ZK_CUDA(cudaStreamSynchronize(C.cur)); // header[] is a stack buffer
+    }
     return zkgpu_extend_and_merkelize(nullptr, image + 2, image + 2 + n_pols * n_ext, const_pols, n_ext, n, n_pols);
 }
 
