@@ -169,7 +169,8 @@ def cpu_sample(args, steps, warmup):
             "sample": "extrapolated: extendPol at full height 2^%d on a %d-column strip (linear in columns) + merkletree at full width "
                       "%d on 2^%d extended rows (linear in rows), blowup %d, %d step(s)" % (args.log_rows, c_l, c, args.cpu_log_rows + args.log_blowup, b, steps),
             "lde_ms": 1e3 * t_l / (n_l * c_l) * cells, "merkletree_ms": 1e3 * t_m / (n_m * c) * cells, "ms_per_step": 1e3 * per_cell * cells,
-            "measured_s_per_sample": t_l + t_m}
+            "measured_s_per_sample": t_l + t_m, "measured_lde_s": t_l, "measured_merkletree_s": t_m,
+            "extrapolated": True}
 
 
 def run_reference(args):
@@ -185,6 +186,8 @@ def run_reference(args):
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "stages_ms": {"STARK_STEP_1_LDE": r["lde_ms"], "STARK_STEP_1_MERKLETREE": r["merkletree_ms"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "measured_s_per_sample": r["measured_s_per_sample"], "measured_lde_s": r["measured_lde_s"],
+            "measured_merkletree_s": r["measured_merkletree_s"], "extrapolated": True,
             "gpu_launches": 0, "wall_s": time.time() - t0}
     print(json.dumps(line), flush=True)
 
@@ -199,6 +202,52 @@ def known_roots():
         d = json.loads(p.read_text())
         out[(d["log_rows"], d["cols"], d["log_blowup"])] = " ".join(d["root"])
     return out
+
+
+def pin_for(log_rows, cols, log_blowup):
+    p = ROOT / "tests" / "golden" / "headline_pin.json"
+    if not p.exists():
+        return None
+    d = json.loads(p.read_text())
+    return d if (d["log_rows"], d["cols"], d["log_blowup"]) == (log_rows, cols, log_blowup) else None
+
+
+def check_pin(pin, zk, torch, dist, world, rank, n_ext, c, d_tree, rows_ptr, row0, nrows):
+    """Compare the committed result with the samples the COMPILED REFERENCE produced (tests/golden/headline_pin.json):
+    on every rank the sampled rows of the extended trace that fall in its row shard [row0, row0 + nrows) at device address
+    rows_ptr, on rank 0 the sampled leaves (level 0) and the sampled nodes of every level of the gathered tree.
+    Covers what root_ok cannot see: the level slices stitched into rank 0's tree and the row shards."""
+    import numpy as np
+    hexw = lambda ws: np.array([int(w, 16) for w in ws], dtype=np.uint64)
+    rows_ok, nrows_checked = True, 0
+    buf = np.zeros(c, dtype=np.uint64)
+    for idx, words in zip(pin["rows"]["index"], pin["rows"]["words"]):
+        if row0 <= idx < row0 + nrows:
+            zk._check(zk.lib().zkgpu_memcpy(buf.ctypes.data, rows_ptr + 8 * (idx - row0) * c, 8 * c))
+            rows_ok = rows_ok and bool(np.array_equal(buf, hexw(words)))
+            nrows_checked += 1
+    leaves_ok = levels_ok = True
+    nleaves = nnodes = 0
+    if rank == 0:
+        off = 0
+        for lv in pin["levels"]:
+            idx = torch.tensor(lv["index"], device="cuda")
+            got = d_tree[off: off + lv["nodes"] * 4].view(-1, 4)[idx].cpu().numpy().view(np.uint64).reshape(-1)
+            ok = bool(np.array_equal(got, hexw([w for dg in lv["digests"] for w in dg])))
+            if lv["level"] == 0:
+                leaves_ok, nleaves = ok, len(lv["index"])
+            else:
+                levels_ok, nnodes = levels_ok and ok, nnodes + len(lv["index"])
+            off += lv["nodes"] * 4
+    flags = torch.tensor([int(rows_ok), nrows_checked], dtype=torch.int64, device="cuda")
+    if world > 1:
+        allf = [torch.zeros_like(flags) for _ in range(world)]
+        dist.all_gather(allf, flags)
+        rows_ok = all(int(f[0]) == 1 for f in allf)
+        nrows_checked = sum(int(f[1]) for f in allf)
+    return {"rows_ok": rows_ok, "leaves_ok": leaves_ok, "levels_ok": levels_ok,
+            "checked": {"rows": nrows_checked, "leaves": nleaves, "nodes_above_leaves": nnodes, "levels": len(pin["levels"])},
+            "source": "compiled reference, tests/golden/headline_pin.json"}
 
 
 def run_ours(args):
@@ -312,6 +361,17 @@ def run_ours(args):
     root = None
     if rank == 0:
         root = " ".join("%016x" % (int(x) & (2**64 - 1)) for x in d_tree[-4:].cpu().tolist())
+    parity_pin = None
+    pin = pin_for(args.log_rows, c, args.log_blowup)
+    if pin is not None:
+        if world == 1:
+            parity_pin = check_pin(pin, zk, torch, dist, 1, 0, n_ext, c, d_tree, d_ext.data_ptr(), 0, n_ext)
+        else:
+            zk.sync()
+            p_rows, R, cc, _ = cd.rows()
+            assert cc == c and R * world == n_ext
+            parity_pin = check_pin(pin, zk, torch, dist, world, rank, n_ext, c, d_tree, p_rows, rank * R, R)
+        del pin
 
     # ---- end to end through the C ABI with HOST buffers (pinned): H2D of the trace and D2H of the tree every step,
     # the extended trace stays resident on the device (what getGroupProof / stage 4 read later).
@@ -351,9 +411,10 @@ def run_ours(args):
         e2e_ms = max_over_ranks(x0.elapsed_time(x1)) / args.e2e_steps
         e2e = {"value": cells / e2e_ms / 1e3, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
-               "label": "resident",
+               "label": "resident" if world == 1 else "resident, pre-sharded input",
                "note": "host pinned trace -> device every step, tree -> host every step; extended trace stays device-resident (see e2e_full_host "
-                       "for the all-host call)"}
+                       "for the all-host call)" + ("" if world == 1 else "; every rank's column pieces were packed into contiguous pinned buffers "
+                       "BEFORE the timed region (1-D copies), a caller holding one row-major trace pays strided copies instead")}
         if rank == 0:
             got = " ".join("%016x" % (int(x) & (2**64 - 1)) for x in h_tree[-4:].tolist())
             assert got == root, "e2e root differs from the device-resident run"
@@ -390,7 +451,8 @@ def run_ours(args):
                 f_ms = f0.elapsed_time(f1) / steps_f
                 got = " ".join("%016x" % (int(x) & (2**64 - 1)) for x in h_tree[-4:].tolist())
                 e2e_full = {"value": cells / f_ms / 1e3, "unit": UNIT, "ms_per_step": f_ms, "h2d_bytes_per_step": cells * 8,
-                            "d2h_bytes_per_step": ext_bytes + h_tree.numel() * 8, "steps": steps_f, "root_ok": got == root,
+                            "d2h_bytes_per_step": ext_bytes + h_tree.numel() * 8, "steps": steps_f,
+                            "root_ok": got == known_roots().get((args.log_rows, c, args.log_blowup), root),
                             "note": "pinned host trace in; extended trace AND tree back to pinned host memory every step"}
             finally:
                 zk.lib().zkgpu_free_host(p_ext)
@@ -510,7 +572,7 @@ def run_ours(args):
                           "STARK_STEP_1_MERKLETREE": (stages.get("leaves") or 0) + (stages.get("nodes") or 0)},
             "roofline": roofline, "roofline_lde": roofline_lde, "cpu_baseline": cpu, "e2e": e2e, "e2e_full_host": e2e_full,
             "small_configs": small, "gpu_launches": int(launches),
-            "clocks": clocks, "root": root}
+            "clocks": clocks, "root": root, "parity_pin": parity_pin}
     want = known_roots().get((args.log_rows, c, args.log_blowup))
     if want is not None:
         line["root_ok"] = (root == want)

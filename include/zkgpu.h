@@ -237,7 +237,10 @@ int zkgpu_dist_plan(uint64_t ncols, int world, int host_input, int *rounds, uint
 int zkgpu_dist_commit(void *ntt, uint64_t *tree, const uint64_t *const *pieces, const uint64_t *piece_ld, int host_input, int gather_tree,
                       uint64_t n_extended, uint64_t n, uint64_t ncols);
 int zkgpu_dist_rows(uint64_t **rows, uint64_t *num_rows, uint64_t *num_cols, uint64_t **subtree);
-int zkgpu_dist_finalize(void); /* leave the job: waits for the device, frees the shards and staging buffers, destroys the communicator(s) */
+/* leave the job: waits for the device, frees the shards and staging buffers, destroys the communicator(s).  In the
+ * process-per-GPU form this is COLLECTIVE: every rank calls it (the ranks meet between closing their mappings of the peers'
+ * row shards and freeing their own, so that nobody frees memory a peer still has open). */
+int zkgpu_dist_finalize(void);
 
 #ifdef __cplusplus
 }

@@ -39,7 +39,6 @@ static int ctx_create(Ctx &C)
     ZK_CUDA(cudaStreamCreateWithFlags(&C.own, cudaStreamNonBlocking));
     C.cur = C.own;
     for (auto &ev : C.ev) ZK_CUDA(cudaEventCreate(&ev));
-    ZK_CUDA(cudaEventCreateWithFlags(&C.tab_ev, cudaEventDisableTiming));
     C.ready = true;
     return 0;
 }

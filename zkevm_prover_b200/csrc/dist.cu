@@ -355,6 +355,18 @@ static int dist_setup_rows(Ctx &C, Dist &D, u64 need_words)
                 cudaIpcCloseMemHandle(D.ipc_open[g]);
                 D.ipc_open[g] = nullptr;
             }
+    // the old shard is freed below: only after EVERY rank has drained its streams (nobody is still copying into a peer) and
+    // closed its mapping of it.  Every rank takes this path together (same shapes on every rank, call after call).
+    if (D.rows)
+    {
+        if (D.single_process)
+            g_group.barrier();
+        else
+        {
+            ZK_NCCL(g_nccl.AllReduce(D.flag, D.flag + 1, 1, ncclUint64, ncclSum, D.comm, D.cs));
+            ZK_CUDA(cudaStreamSynchronize(D.cs));
+        }
+    }
     const int alloc_rc = dev_realloc(&D.rows, &D.rows_cap, need_words);
     if (D.single_process)
     {
@@ -993,7 +1005,10 @@ int zkgpu_dist_commit(void *, uint64_t *tree, const uint64_t *const *pieces, con
     return dist_commit_rank(C, ps, host_input != 0, n_ext, n, ncols, tree, false, gather_tree != 0, nullptr);
 }
 
-static void dist_destroy(Ctx &C)
+// Leaving a job takes two steps with a meeting of all ranks between them: first every rank drains its streams and closes
+// its mappings of the peers' row shards, then (once EVERY rank has done so) the memory is freed.  Freeing a shard a peer
+// still has open through cudaIpcOpenMemHandle, or is still copying into, is undefined behaviour.
+static void dist_quiesce(Ctx &C)
 {
     Dist *D = C.dist;
     if (!D) return;
@@ -1001,13 +1016,33 @@ static void dist_destroy(Ctx &C)
     cudaStreamSynchronize(D->cs);
     cudaStreamSynchronize(D->xs);
     cudaStreamSynchronize(D->sa);
+    if (C.h2d) cudaStreamSynchronize(C.h2d);
+    if (C.d2h) cudaStreamSynchronize(C.d2h);
     if (!D->single_process)
         for (int g = 0; g < D->world; g++)
-            if (D->ipc_open[g]) cudaIpcCloseMemHandle(D->ipc_open[g]);
+            if (D->ipc_open[g])
+            {
+                cudaIpcCloseMemHandle(D->ipc_open[g]);
+                D->ipc_open[g] = nullptr;
+            }
+}
+static void dist_release(Ctx &C)
+{
+    Dist *D = C.dist;
+    if (!D) return;
     u64 *bufs[] = {D->rows, D->sub, D->top, D->tree_dev, D->in_buf, D->ext_buf, D->recv_buf, D->ipc_scratch, D->flag, D->peer_tab};
     for (u64 *b : bufs)
         if (b) cudaFree(b);
     if (D->comm) g_nccl.CommDestroy(D->comm);
+    cudaEvent_t evs[] = {D->ev_cp, D->ev_sa, D->ev_a, D->ev_b};
+    for (cudaEvent_t e : evs)
+        if (e) cudaEventDestroy(e);
+    for (int i = 0; i < MAX_ROUNDS; i++)
+    {
+        if (D->ev_lde[i]) cudaEventDestroy(D->ev_lde[i]);
+        if (D->ev_bar[i]) cudaEventDestroy(D->ev_bar[i]);
+        if (D->ev_unp[i]) cudaEventDestroy(D->ev_unp[i]);
+    }
     cudaStreamDestroy(D->cs);
     cudaStreamDestroy(D->xs);
     cudaStreamDestroy(D->sa);
@@ -1019,17 +1054,34 @@ int zkgpu_dist_finalize(void)
 {
     if (g_group.n)
     {
+        std::lock_guard<std::mutex> no_commit_running(g_multi_mu);
         for (int g = 0; g < g_group.n; g++)
         {
             Enter en(g_group.ctx[g]->device);
-            if (en.rc >= 0) dist_destroy(*en.c);
+            if (en.rc >= 0) dist_quiesce(*en.c);
+        }
+        for (int g = 0; g < g_group.n; g++)
+        {
+            Enter en(g_group.ctx[g]->device);
+            if (en.rc >= 0) dist_release(*en.c);
         }
         g_group.n = 0;
+        g_exchange = -1;
         zk::Enter back(0);
         return back.rc;
     }
     ZK_ENTER;
-    dist_destroy(C);
+    if (!C.dist) return 0;
+    dist_quiesce(C);
+    if (C.dist->world > 1)
+    {
+        // collective in the process-per-GPU form: every rank of the job calls zkgpu_dist_finalize
+        Dist &D = *C.dist;
+        ZK_NCCL(g_nccl.AllReduce(D.flag, D.flag + 1, 1, ncclUint64, ncclSum, D.comm, D.cs));
+        ZK_CUDA(cudaStreamSynchronize(D.cs));
+    }
+    dist_release(C);
+    g_exchange = -1;
     return 0;
 }
 

@@ -346,9 +346,10 @@ __global__ void build_pow_tables(u64 *G0, u64 *G1, u64 g, u64 scale, u32 n1)
     if (i < n1) G1[i] = gl::mul(scale, dev_pow(g, (u64)i << 12));
 }
 
-// Tables live in the calling thread's context (one set per device).  The build kernel is enqueued on the caller's stream;
-// an event recorded after every build is waited on by every later user, so a table built on one stream is safe to read
-// from another (zkgpu_set_stream).  The cache is bounded: past 96 entries (a blowup-16 LDE needs 18) it is flushed.
+// Tables live in the calling thread's context (one set per device).  The build kernel is enqueued on the caller's stream and
+// every table has its own "built" event: a user on another stream (zkgpu_set_stream, the sponge / exchange streams of the
+// multi-GPU commit) waits for exactly the table it reads, whatever was built in between and wherever.
+// The cache is bounded: past 96 entries (a blowup-16 LDE needs 18) it is flushed.
 int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64 **G1, cudaStream_t st)
 {
     Ctx &C = *t_ctx;
@@ -361,26 +362,29 @@ int get_power_tables(u64 g, u64 scale, unsigned log_n, const u64 **G0, const u64
             ZK_CUDA(cudaDeviceSynchronize());
             for (auto &kv : C.tabs)
             {
-                cudaFree(kv.second.first);
-                cudaFree(kv.second.second);
+                cudaFree(kv.second.g0);
+                cudaFree(kv.second.g1);
+                if (kv.second.built) cudaEventDestroy(kv.second.built);
             }
             C.tabs.clear();
         }
         const u32 n1 = log_n > 12 ? (1u << (log_n - 12)) : 1u;
-        u64 *d0 = nullptr, *d1 = nullptr;
-        ZK_CUDA(cudaMalloc(&d0, 4096 * sizeof(u64)));
-        ZK_CUDA(cudaMalloc(&d1, (size_t)n1 * sizeof(u64)));
+        Ctx::Tab t;
+        ZK_CUDA(cudaMalloc(&t.g0, 4096 * sizeof(u64)));
+        ZK_CUDA(cudaMalloc(&t.g1, (size_t)n1 * sizeof(u64)));
+        ZK_CUDA(cudaEventCreateWithFlags(&t.built, cudaEventDisableTiming));
         const u32 n = n1 > 4096 ? n1 : 4096;
-        build_pow_tables<<<(n + 255) / 256, 256, 0, st>>>(d0, d1, g, scale, n1);
+        build_pow_tables<<<(n + 255) / 256, 256, 0, st>>>(t.g0, t.g1, g, scale, n1);
         ZK_LAUNCHED();
         ZK_CUDA(cudaGetLastError());
-        ZK_CUDA(cudaEventRecord(C.tab_ev, st));
-        it = C.tabs.emplace(key, std::make_pair(d0, d1)).first;
+        ZK_CUDA(cudaEventRecord(t.built, st));
+        t.built_on = st;
+        it = C.tabs.emplace(key, t).first;
     }
-    else
-        ZK_CUDA(cudaStreamWaitEvent(st, C.tab_ev, 0));
-    *G0 = it->second.first;
-    *G1 = it->second.second;
+    else if (it->second.built_on != st)
+        ZK_CUDA(cudaStreamWaitEvent(st, it->second.built, 0));
+    *G0 = it->second.g0;
+    *G1 = it->second.g1;
     return 0;
 }
 

@@ -17,7 +17,6 @@ namespace zk {
 // ---- error plumbing (api.cu) ----
 void set_error(const char *fmt, ...);
 const char *last_error();
-const char *last_error();
 #define ZK_CUDA(call)                                                                              \
     do {                                                                                           \
         cudaError_t e__ = (call);                                                                  \
@@ -67,8 +66,13 @@ struct Ctx
     std::vector<Seg> segs; // segments of the last pipelined call: kind 0 = LDE, 1 = leaf absorption
     // per-device tables and one-time uploads (module globals such as __constant__ arrays exist once per device)
     bool consts_ready = false, w256_ready = false;
-    std::map<std::tuple<u64, u64, unsigned>, std::pair<u64 *, u64 *>> tabs; // get_power_tables cache
-    cudaEvent_t tab_ev = nullptr;                                           // last table build (other streams wait on it)
+    struct Tab
+    {
+        u64 *g0 = nullptr, *g1 = nullptr;
+        cudaEvent_t built = nullptr;     // recorded after this table's build kernel
+        cudaStream_t built_on = nullptr; // users on that stream are ordered behind the build anyway
+    };
+    std::map<std::tuple<u64, u64, unsigned>, Tab> tabs; // get_power_tables cache
     std::map<const void *, int> occupancy;                                  // kernel -> resident CTAs per SM (smem attribute set)
     std::vector<Resident> *resident = nullptr;
     size_t resident_budget = 0;

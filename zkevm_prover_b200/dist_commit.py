@@ -149,8 +149,9 @@ def piece_plan(ncols, world, rounds=None, host_input=True):
     whole number of 8-column sponge blocks; inside a round the columns are dealt out evenly (the extra columns rotate
     over the ranks from round to round).  Returns (rounds, plan) with plan[k][g] = (first column, width).
 
-    host_input=True: the rounds ramp up — 2 blocks per rank, then 4, then equal rounds of at most 8 — so that with a
-    host-resident trace only the copy of the first small piece is exposed; host_input=False: one round.
+    host_input=True: uniform small rounds — two sponge blocks (16 columns) per rank and round, wider only when that would take
+    more than 14 rounds — so that little is left to compute after the last host copy lands; host_input=False: one round
+    (peer stores) or two (staged exchange).  The library decides (csrc/dist.cu make_plan); this only asks it.
     An explicit `rounds` gives equal rounds (test hook, Python model only)."""
     if rounds is None:
         import ctypes
