@@ -1,5 +1,6 @@
 // pos_bench.cu — Poseidon permutation throughput of the library's own code under compile-time variants
 // (development aid).  nvcc ... -DZK_POS_FP64=f -DZK_CONV_IN=i -DZK_CONV_OUT=o -o tools/pos_bench_fio tools/pos_bench.cu
+#define ZK_NO_ENTRY_POINTS
 #include "../zkevm_prover_b200/csrc/poseidon.cu"
 #include <cstdio>
 #include <cstdarg>
@@ -35,7 +36,7 @@ int main()
         cudaEventElapsedTime(&ms, e0, e1);
         if (ms < best) best = ms;
     }
-    printf("MDS_FFT=%d POS_FP64=%d CONV_IN=%d CONV_OUT=%d MDS_ASM=%d SBOX_ROLL=%d kat=%s  %.3f ms for 2^22 permutations = %.1f Mperm/s\n", ZK_MDS_FFT, ZK_POS_FP64, ZK_CONV_IN, ZK_CONV_OUT, ZK_MDS_ASM, ZK_SBOX_ROLL, ok ? "ok" : "FAIL", best,
+    printf("MIN_CTAS=%d MDS_FFT=%d POS_FP64=%d CONV_IN=%d CONV_OUT=%d MDS_ASM=%d SBOX_ROLL=%d kat=%s  %.3f ms for 2^22 permutations = %.1f Mperm/s\n", ZK_POS_MIN_CTAS, ZK_MDS_FFT, ZK_POS_FP64, ZK_CONV_IN, ZK_CONV_OUT, ZK_MDS_ASM, ZK_SBOX_ROLL, ok ? "ok" : "FAIL", best,
            n / best / 1e3);
     return ok ? 0 : 1;
 }

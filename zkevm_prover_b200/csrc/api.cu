@@ -243,7 +243,7 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
         // with a device-resident extended trace most of the memory belongs to the caller: stay small.  With a host-resident
         // one the strips are all the library holds, and wide strips are what the copies want (rows of 384 B moved at
         // 29 GB/s up and 36 GB/s down, profiles/r2_e2e_full_trace.txt; the strided copies reach the link rate from ~900 B)
-        const size_t cap = (size_t)(out_dev ? 24 : 72) << 30;
+        const size_t cap = (size_t)(out_dev ? 24 : (getenv("ZKGPU_HOST_STRIP") ? 112 : 72)) << 30;
         if (budget > cap) budget = cap;
         w = budget / (per_col * sizeof(u64));
     }
@@ -251,6 +251,8 @@ static int commit_pipeline(Ctx &C, u64 *out_ext, bool out_dev, u64 *d_tree, cons
     {
         // enough strips for the copies to overlap the compute
         u64 target = ((ncols + 5) / 6 + 15) & ~(u64)15;
+        if (const char *e = getenv("ZKGPU_HOST_STRIP")) // development knob (tools/host_strip_sweep.py): strip width in columns
+            if (atoi(e) >= 16) target = (u64)atoi(e) & ~(u64)15;
         if (target < 16) target = 16;
         if (w > target) w = target;
     }

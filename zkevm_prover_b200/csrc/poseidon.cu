@@ -553,7 +553,12 @@ __device__ __forceinline__ void poseidon_permute_state(u64 (&st)[12])
 // ---------------------------------------------------------------------------------------------------
 // kernels
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) permute_kernel(u64 *out, const u64 *in, u64 n)
+// ZK_POS_MIN_CTAS (experiment knob, tools/pos_bench.cu): minimum resident CTAs per SM asked of ptxas for the 128-thread hash
+// kernels.  Unset, ptxas is free to use up to 255 registers and settles on 72 (7 CTAs per SM) — it is not squeezed.
+#ifndef ZK_POS_MIN_CTAS
+#define ZK_POS_MIN_CTAS 1
+#endif
+__global__ void __launch_bounds__(128, ZK_POS_MIN_CTAS) permute_kernel(u64 *out, const u64 *in, u64 n)
 {
     const u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -878,6 +883,7 @@ static int static_digests(Ctx &C, u64 **addr)
 
 } // namespace zk
 
+#ifndef ZK_NO_ENTRY_POINTS // tools/pos_bench.cu includes this file on its own, without the context code of ctx.cu
 extern "C" int zkgpu_merkletree_batch_noalloc(uint64_t *tree, const uint64_t *input, uint64_t ncols, uint64_t nrows, uint64_t batch,
                                               uint64_t dim)
 {
@@ -922,3 +928,4 @@ extern "C" int zkgpu_merkletree_batch_noalloc(uint64_t *tree, const uint64_t *in
     ZK_CUDA(cudaGetLastError());
     return merkle_levels(tree, nrows, st);
 }
+#endif
