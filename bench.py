@@ -481,13 +481,15 @@ def run_ours(args):
                 t_enq = min(t_enq, time.perf_counter() - t0)
             torch.cuda.synchronize()
             g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            l0 = zk.lib().zkgpu_launch_count()
             g0.record(stream)
             for _ in range(reps):
                 zk.extend_and_merkelize(s_ntt, s_ext, s_tree, s_in, ne, nn, cc)
             g1.record(stream)
+            l1 = zk.lib().zkgpu_launch_count()
             torch.cuda.synchronize()
             ms = g0.elapsed_time(g1) / reps
-            small[name] = {"ms_per_commit": ms, "Mcells_per_s": nn * cc / ms / 1e3, "host_enqueue_ms": 1e3 * t_enq, "launches_per_commit": None,
+            small[name] = {"ms_per_commit": ms, "Mcells_per_s": nn * cc / ms / 1e3, "host_enqueue_ms": 1e3 * t_enq, "launches_per_commit": (l1 - l0) / reps,
                            "root": " ".join("%016x" % (int(x) & (2**64 - 1)) for x in s_tree[-4:].cpu().tolist())}
             del s_in, s_ext, s_tree
 

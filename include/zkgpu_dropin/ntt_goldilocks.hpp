@@ -12,6 +12,8 @@
 //   * errors throw std::runtime_error instead of assert()/undefined behaviour.
 #ifndef NTT_GOLDILOCKS
 #define NTT_GOLDILOCKS
+#include <atomic>
+#include <cstdio>
 #include "goldilocks_element.hpp"
 #include <sys/types.h>
 
@@ -59,6 +61,16 @@ public:
     {
         (void)nphase;
         (void)nblock;
+        // FRI's folding loop (friProve.cpp:44-102) runs one tiny INTT per group from inside an OpenMP region: through this class
+        // every one of them is a host-pointer call (lock, copy in, launch, copy out, synchronise), serialised on the device's
+        // context — correct, but far slower than the CPU was.  Say so once; zkgpu_fri_fold does a whole layer in one call.
+        if (size <= 64 && ncols <= 4)
+        {
+            static std::atomic<unsigned> tiny{0};
+            if (tiny.fetch_add(1, std::memory_order_relaxed) == 1024)
+                fprintf(stderr, "[zkgpu] 1024 transforms of <= 64 rows x <= 4 columns went through NTT_Goldilocks one by one; if this is "
+                                "FRIProve::prove's folding loop, call zkgpu_fri_fold per layer instead (INTEGRATION.md section 2)\n");
+        }
         zkgpu_dropin::check(zkgpu_ntt(h, zkgpu_dropin::words(dst), zkgpu_dropin::words(src), size, ncols, zkgpu_dropin::words(buffer),
                                       inverse ? 1 : 0, extend ? 1 : 0),
                             "NTT_Goldilocks::NTT");

@@ -60,6 +60,10 @@ public:
     static void merkletree_batch_seq(E *t, E *i, uint64_t c, uint64_t r, uint64_t b, int nt = 0, uint64_t d = 1) { merkletree_batch(t, i, c, r, b, nt, d); }
     static void merkletree_batch_avx(E *t, E *i, uint64_t c, uint64_t r, uint64_t b, int nt = 0, uint64_t d = 1) { merkletree_batch(t, i, c, r, b, nt, d); }
 #ifdef __AVX512__
+    // poseidon_goldilocks.hpp:64-66 (dead in the shipped AVX2 build, Makefile:31-37; present so that an AVX-512 build links)
+    static void hash_full_result_avx512(E *s, const E *i) { hash_full_result(s, i); }
+    static void hash_avx512(E (&s)[CAPACITY], const E (&i)[SPONGE_WIDTH]) { hash(s, i); }
+    static void linear_hash_avx512(E *o, E *i, uint64_t n) { linear_hash(o, i, n); }
     static void merkletree_avx512(E *t, E *i, uint64_t c, uint64_t r, int nt = 0, uint64_t d = 1) { merkletree(t, i, c, r, nt, d); }
     static void merkletree_batch_avx512(E *t, E *i, uint64_t c, uint64_t r, uint64_t b, int nt = 0, uint64_t d = 1) { merkletree_batch(t, i, c, r, b, nt, d); }
 #endif
