@@ -529,6 +529,17 @@ def run_ours(args):
     # (profiles/r1_int_bench_fp64.txt: IMAD.WIDE/IMAD.HI occupy it 4 clocks per warp instruction, DFMA/DADD 2).  One
     # permutation needs at least 472 products x (4 IMAD.WIDE + 1 IMAD.HI) and 8 x 156 + 11 x 256 FP64 operations on it
     #  = 17568 clocks per warp of 32 permutations; the peak below is that bound at the measured SM clock.
+    # pipe rates of THIS GPU in THIS run (zkgpu_pipe_probe, csrc/probe.cu): thread-instructions per second, whole GPU
+    pipe = None
+    try:
+        pr = (ctypes.c_double * 8)()
+        zk._check(zk.lib().zkgpu_pipe_probe(pr))
+        zk.sync()
+        pipe = {"imad_wide": pr[0], "iadd3": pr[1], "dfma": pr[2], "dfma_plus_imad_wide_1to1": pr[3], "gl_mul_nc": pr[4], "butterfly": pr[5],
+                "unit": "thread-instructions (operations for gl_mul_nc, butterfly) per second per GPU", "sms": int(pr[6]),
+                "source": "measured in this run, register-only loops, 32 warps/SM (csrc/probe.cu)"}
+    except Exception as e:  # the probe is evidence, not the product: say why it is missing
+        pipe = {"error": str(e)}
     port_clocks = 472 * 5 * 4 + (8 * 156 + 11 * 256) * 2
     if roofline["permutations_per_s"]:
         sm_clock = 1.965e9
@@ -539,7 +550,26 @@ def run_ours(args):
         peak_perm = 148 * 4 * sm_clock / port_clocks * 32
         roofline["arithmetic"] = {"bound": "IMAD+FP64 dispatch port", "achieved": roofline["permutations_per_s"], "peak": peak_perm,
                                   "unit": "permutations/s per GPU", "frac": roofline["permutations_per_s"] / peak_perm,
-                                  "port_clocks_per_warp_permutation": port_clocks}
+                                  "port_clocks_per_warp_permutation": port_clocks,
+                                  "peak_source": "model: 4 port clocks per IMAD.WIDE/IMAD.HI warp instruction, 2 per DFMA/DADD, at the sampled SM clock"}
+        if pipe and "imad_wide" in pipe:
+            # the same operation counts (472 products x 5 multiplier instructions, 8 x 156 + 11 x 256 FP64 operations per permutation,
+            # DESIGN.md section 3) priced with the MEASURED rates.  The two pipes share a dispatch port when the 1:1 mix runs no
+            # faster than the sum of the separate times; if it does run faster they overlap and only the longer one counts.
+            n_mul, n_fp = 472 * 5, 8 * 156 + 11 * 256
+            t_mul, t_fp = n_mul / pipe["imad_wide"], n_fp / pipe["dfma"]
+            t_mix_pair = 2.0 / pipe["dfma_plus_imad_wide_1to1"]                      # one DFMA + one IMAD.WIDE, interleaved
+            t_sep_pair = 1.0 / pipe["imad_wide"] + 1.0 / pipe["dfma"]
+            # overlap factor of the two pipes as measured by the 1:1 mix: 1.0 = fully serialised on a shared port, down to
+            # max/(sum) = fully overlapped.  The peak prices the permutation's two instruction streams with that factor.
+            overlap = min(1.0, max(t_mix_pair / t_sep_pair, max(t_mul, t_fp) / (t_mul + t_fp)))
+            peak_meas = 1.0 / ((t_mul + t_fp) * overlap)
+            roofline["arithmetic"]["measured"] = {"peak": peak_meas, "frac": roofline["permutations_per_s"] / peak_meas,
+                                                   "mix_over_separate": t_mix_pair / t_sep_pair, "overlap_factor_used": overlap,
+                                                   "multiplier_instructions_per_permutation": n_mul, "fp64_operations_per_permutation": n_fp,
+                                                   "note": "peak = 1 / ((multiplier instructions / measured IMAD.WIDE rate + FP64 operations / measured DFMA "
+                                                           "rate) x overlap), overlap = time of the interleaved 1:1 mix over the sum of the separate times "
+                                                           "(1.0 = one shared dispatch port, fully serialised)"}
     lde_ms = stages.get("lde")
     lde_bytes = 8 * c * (n + n_ext) / world
     roofline_lde = {"stage": "extendPol (INTT + coset NTTs, all passes)", "bound": "hbm",
@@ -556,7 +586,17 @@ def run_ours(args):
         alu_rate = cells / world * alu_per_cell / (lde_ms * 1e-3)
         roofline_lde["arithmetic"] = {"bound": "ALU pipe (IADD3/LOP3/SHF/SEL)", "alu_instructions_per_cell": alu_per_cell, "achieved": alu_rate,
                                       "peak": alu_peak, "unit": "ALU thread-instructions/s per GPU", "frac": alu_rate / alu_peak,
-                                      "source": "instruction counts from the committed ncu capture, rate measured in this run"}
+                                      "source": "instruction counts from profiles/r1_ncu_full_2p20x665_v3.csv (154 per element-pass, 53 % ALU-pipe); "
+                                                "peak = 64 ALU lanes per SM at the sampled clock (model)"}
+        if pipe and "iadd3" in pipe:
+            # measured ALU-pipe rate instead of the 64-lane model, and the synthetic ceiling of the butterflies themselves: the
+            # transform needs (1 INTT + 2 coset NTTs of size N) = 3 * N/2 * log2 N butterflies per column at blowup 2; the probe's
+            # butterfly loop (general twiddle, registers only, no loads, no index arithmetic) bounds how fast they can possibly go
+            bf = 3.0 * (n / 2) * args.log_rows * c / world
+            roofline_lde["arithmetic"]["measured"] = {"peak": pipe["iadd3"], "frac": alu_rate / pipe["iadd3"]}
+            roofline_lde["synthetic_butterfly_ceiling"] = {"butterflies": bf, "butterflies_per_s": pipe["butterfly"],
+                                                           "floor_ms": 1e3 * bf / pipe["butterfly"], "frac": (1e3 * bf / pipe["butterfly"]) / lde_ms,
+                                                           "note": "floor_ms = butterflies / measured register-only butterfly rate; frac = floor / measured LDE time"}
 
     cpu = None
     if not args.no_cpu and world == 1:
@@ -574,7 +614,7 @@ def run_ours(args):
                           "STARK_STEP_1_MERKLETREE": (stages.get("leaves") or 0) + (stages.get("nodes") or 0)},
             "roofline": roofline, "roofline_lde": roofline_lde, "cpu_baseline": cpu, "e2e": e2e, "e2e_full_host": e2e_full,
             "small_configs": small, "gpu_launches": int(launches),
-            "clocks": clocks, "root": root, "parity_pin": parity_pin}
+            "clocks": clocks, "root": root, "parity_pin": parity_pin, "pipe_rates": pipe}
     want = known_roots().get((args.log_rows, c, args.log_blowup))
     if want is not None:
         line["root_ok"] = (root == want)

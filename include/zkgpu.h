@@ -40,6 +40,12 @@ int zkgpu_mem_info(uint64_t *free_bytes, uint64_t *total_bytes);
 /* tuning / experiment hook: key 0 = threads per CTA of the sponge kernel (128 | 512), key 2 = commit cache on/off, key 1 = cap on transform threads per
  * SM (0 = none).  Used by tools/overlap_probe.py; not needed in normal use. */
 int zkgpu_tune(int key, int value);
+/* measurement hook (bench.py): sustained rates of this GPU's pipes, in thread-instructions (or operations) per second for the
+ * whole GPU, from register-only loops of 8 independent chains at 32 warps per SM (csrc/probe.cu; ~30 ms):
+ * out[0] IMAD.WIDE.U32, [1] IADD3 (ALU pipe), [2] DFMA, [3] DFMA and IMAD.WIDE interleaved 1:1 (both counted), [4] gl::mul_nc
+ * (un-normalised 64-bit modular multiplies), [5] radix-2 butterflies (modular multiply + add + sub), [6] SM count, [7] 0.
+ * The arithmetic roofs in the bench line are derived from these, measured in the same run.  No counterpart in the reference. */
+int zkgpu_pipe_probe(double out[8]);
 /* device-memory helpers so that C/C++ hosts need no CUDA headers */
 int zkgpu_malloc(void **dev_ptr, uint64_t bytes);
 int zkgpu_free(void *dev_ptr);

@@ -72,6 +72,7 @@ ABI_SYMBOLS = {
     "zkgpu_merkle_levels": (_int, [_vp, _u64]),
     "zkgpu_copy_block": (_int, [_vp, _u64, _vp, _u64, _u64, _u64]),
     "zkgpu_invalidate": (_int, [_vp]),
+    "zkgpu_pipe_probe": (_int, [ctypes.POINTER(ctypes.c_double)]),
     "zkgpu_cache_stats": (_int, [ctypes.POINTER(_u64)]),
     "zkgpu_stage4_commit": (_int, [_vp, _vp, _vp, _vp, _u64, _u64, _u64, _u64]),
     "zkgpu_init_multi": (_int, [_int]),
